@@ -1,0 +1,361 @@
+// K2: per-row concept injection fused into the next RMSNorm (sm_100a).
+//
+// One warp owns one (row, position) vector of the residual stream.  The vector is read once with
+// coalesced vector loads, kept packed in registers across the reduction, and written back once
+// (h', only if steered) plus once (y).  HBM traffic is the algorithmic minimum
+// rows*T*H*e*(2 reads + 2 writes) + H*e; the concept table (<= 0.5 MB) and the norm weight live in
+// L2 / shared memory.  No tensor-core work: < 2 flop/byte.
+//
+// Summation order of the variance (part of the numeric contract, see include/ia_b200.h and
+// oracle/kernels_np.py:row_sum_squares): lane l owns the 4-element groups l, l+32, l+64, ...;
+// one fp32 accumulator per element slot, groups added in ascending order; accumulators combined
+// ((a0+a1)+a2)+a3; lanes combined by shuffle-down 16, 8, 4, 2, 1.  This is ATen's CUDA order for a
+// contiguous fp32 [R>=16, H] mean(-1), which makes the kernel bit-identical to the eager chain
+// hook-add -> .float() -> pow(2) -> mean -> +eps -> rsqrt -> mul -> .to(dtype) -> * weight.
+// Every product and sum that torch rounds separately is issued as __fmul_rn/__fadd_rn so the
+// compiler cannot contract them into an FMA.
+
+#include "ia_common.cuh"
+
+namespace ia {
+
+struct K2Params {
+    void *h;            // [nvec, H] in/out (TAIL: residual in/out)
+    void *y;            // [nvec, H] out
+    const void *mlp;    // TAIL only: [nvec, H] MLP output
+    const void *vtable; // [n_vec, H]
+    const int32_t *row_vec;
+    const float *row_alpha;
+    const int32_t *row_t0;
+    const void *w;      // next norm weight [H]
+    const void *w_post; // TAIL only: post-feedforward norm weight [H]
+    float eps;
+    float inv_h;
+    int nvec;  // rows * T
+    int T;
+    int H;
+    int pos0;
+    int steer_all;
+};
+
+template <bool IEEE> __device__ __forceinline__ float rinv(float var, float eps) {
+    float t = __fadd_rn(var, eps);
+    if (IEEE) return __fdiv_rn(1.0f, __fsqrt_rn(t));
+    return rsqrtf(t);
+}
+
+__device__ __forceinline__ float warp_total(float a0, float a1, float a2, float a3) {
+    float s = __fadd_rn(__fadd_rn(__fadd_rn(a0, a1), a2), a3);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s = __fadd_rn(s, __shfl_down_sync(FULL, s, off));
+    return __shfl_sync(FULL, s, 0);
+}
+
+template <typename T, int VARIANT> __device__ __forceinline__ float norm_out(float x, float r, float w) {
+    float n = __fmul_rn(x, r);
+    if (VARIANT == IA_NORM_LLAMA) return Elt<T>::rd(__fmul_rn(w, Elt<T>::rd(n)));
+    return Elt<T>::rd(__fmul_rn(n, __fadd_rn(1.0f, w)));
+}
+
+// Register-resident implementation: MAXJ = groups of 4 elements per lane (H <= 128 * MAXJ).
+template <typename T, typename VT, int MAXJ, int VARIANT, bool IEEE, bool TAIL, int MINB>
+__global__ void __launch_bounds__(128, MINB) k2_regs_kernel(const K2Params p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T *w_s = reinterpret_cast<T *>(smem_raw);
+    T *wpost_s = w_s + p.H;  // TAIL only
+    const int H = p.H;
+    {
+        // cooperative 8-byte copies of the weight(s) into shared memory
+        const int n4 = H >> 2;
+        for (int g = threadIdx.x; g < n4; g += blockDim.x) {
+            st4<T>(w_s + 4 * g, ld4_ro<T>(static_cast<const T *>(p.w) + 4 * g));
+            if (TAIL) st4<T>(wpost_s + 4 * g, ld4_ro<T>(static_cast<const T *>(p.w_post) + 4 * g));
+        }
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const int warps_per_cta = blockDim.x >> 5;
+    const int G = H >> 2;
+    T *hbase = static_cast<T *>(p.h);
+    T *ybase = static_cast<T *>(p.y);
+
+    for (int vec = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); vec < p.nvec; vec += gridDim.x * warps_per_cta) {
+        const int row = vec / p.T;
+        const int pos = vec - row * p.T;
+        const int vi = p.row_vec ? __ldg(p.row_vec + row) : -1;
+        const bool steer = vi >= 0 && (p.steer_all || (pos + p.pos0 >= __ldg(p.row_t0 + row)));
+        const float alpha = steer ? __ldg(p.row_alpha + row) : 0.0f;
+        T *hp = hbase + (size_t)vec * H;
+
+        Pack4<T> x[MAXJ];
+        if (!TAIL) {
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j) {
+                const int g = lane + 32 * j;
+                if (g < G) x[j] = ld4<T>(hp + 4 * g);
+            }
+        } else {
+            // Gemma-2 block tail: h = rd(residual + gemma_norm(mlp_out; w_post))
+            const T *mp = static_cast<const T *>(p.mlp) + (size_t)vec * H;
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j) {
+                const int g = lane + 32 * j;
+                if (g < G) x[j] = ld4_ro<T>(mp + 4 * g);
+            }
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j) {
+                const int g = lane + 32 * j;
+                if (g < G) {
+                    float f[4];
+                    Elt<T>::unpack(x[j], f);
+                    a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
+                    a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
+                    a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
+                    a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
+                }
+            }
+            const float rm = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j) {
+                const int g = lane + 32 * j;
+                if (g < G) {
+                    float f[4], wf[4], rf[4];
+                    Elt<T>::unpack(x[j], f);
+                    Elt<T>::unpack(ld4<T>(wpost_s + 4 * g), wf);
+                    Elt<T>::unpack(ld4<T>(hp + 4 * g), rf);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        f[i] = Elt<T>::rd(__fadd_rn(rf[i], norm_out<T, IA_NORM_GEMMA>(f[i], rm, wf[i])));
+                    Elt<T>::pack_exact(f, x[j]);
+                }
+            }
+        }
+
+        if (steer) {
+            const VT *vp = static_cast<const VT *>(p.vtable) + (size_t)vi * H;
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j) {
+                const int g = lane + 32 * j;
+                if (g < G) {
+                    float f[4], vf[4];
+                    Elt<T>::unpack(x[j], f);
+                    Elt<VT>::unpack(ld4_ro<VT>(vp + 4 * g), vf);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        f[i] = Elt<T>::rd(__fadd_rn(f[i], Elt<T>::rd(__fmul_rn(vf[i], alpha))));
+                    Elt<T>::pack_exact(f, x[j]);
+                    st4<T>(hp + 4 * g, x[j]);
+                }
+            }
+        } else if (TAIL) {
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j) {
+                const int g = lane + 32 * j;
+                if (g < G) st4<T>(hp + 4 * g, x[j]);
+            }
+        }
+
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+        for (int j = 0; j < MAXJ; ++j) {
+            const int g = lane + 32 * j;
+            if (g < G) {
+                float f[4];
+                Elt<T>::unpack(x[j], f);
+                a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
+                a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
+                a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
+                a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
+            }
+        }
+        const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
+
+        T *yp = ybase + (size_t)vec * H;
+#pragma unroll
+        for (int j = 0; j < MAXJ; ++j) {
+            const int g = lane + 32 * j;
+            if (g < G) {
+                float f[4], wf[4];
+                Elt<T>::unpack(x[j], f);
+                Elt<T>::unpack(ld4<T>(w_s + 4 * g), wf);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) f[i] = norm_out<T, VARIANT>(f[i], r, wf[i]);
+                Pack4<T> out;
+                Elt<T>::pack_exact(f, out);
+                st4<T>(yp + 4 * g, out);
+            }
+        }
+    }
+}
+
+// Any H % 4 == 0: two passes over the row; the second pass re-reads h' (L1/L2 hit).
+template <typename T, typename VT, int VARIANT, bool IEEE>
+__global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
+    const int lane = threadIdx.x & 31;
+    const int warps_per_cta = blockDim.x >> 5;
+    const int H = p.H, G = H >> 2;
+    T *hbase = static_cast<T *>(p.h);
+    T *ybase = static_cast<T *>(p.y);
+    const T *w = static_cast<const T *>(p.w);
+    for (int vec = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); vec < p.nvec; vec += gridDim.x * warps_per_cta) {
+        const int row = vec / p.T;
+        const int pos = vec - row * p.T;
+        const int vi = p.row_vec ? __ldg(p.row_vec + row) : -1;
+        const bool steer = vi >= 0 && (p.steer_all || (pos + p.pos0 >= __ldg(p.row_t0 + row)));
+        const float alpha = steer ? __ldg(p.row_alpha + row) : 0.0f;
+        T *hp = hbase + (size_t)vec * H;
+        const VT *vp = static_cast<const VT *>(p.vtable) + (size_t)(steer ? vi : 0) * H;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        for (int g = lane; g < G; g += 32) {
+            float f[4];
+            Elt<T>::unpack(ld4<T>(hp + 4 * g), f);
+            if (steer) {
+                float vf[4];
+                Elt<VT>::unpack(ld4_ro<VT>(vp + 4 * g), vf);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    f[i] = Elt<T>::rd(__fadd_rn(f[i], Elt<T>::rd(__fmul_rn(vf[i], alpha))));
+                Pack4<T> o;
+                Elt<T>::pack_exact(f, o);
+                st4<T>(hp + 4 * g, o);
+            }
+            a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
+            a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
+            a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
+            a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
+        }
+        const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
+        T *yp = ybase + (size_t)vec * H;
+        for (int g = lane; g < G; g += 32) {
+            float f[4], wf[4];
+            Elt<T>::unpack(ld4<T>(hp + 4 * g), f);  // own earlier store, or untouched input
+            Elt<T>::unpack(ld4_ro<T>(w + 4 * g), wf);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) f[i] = norm_out<T, VARIANT>(f[i], r, wf[i]);
+            Pack4<T> o;
+            Elt<T>::pack_exact(f, o);
+            st4<T>(yp + 4 * g, o);
+        }
+    }
+}
+
+static int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+template <typename T, typename VT, int MAXJ, int VARIANT, bool IEEE, bool TAIL, int MINB>
+static int launch_regs(const K2Params &p, cudaStream_t s) {
+    auto kern = k2_regs_kernel<T, VT, MAXJ, VARIANT, IEEE, TAIL, MINB>;
+    const size_t smem = (size_t)p.H * sizeof(T) * (TAIL ? 2 : 1);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+    }
+    const int warps = 4;
+    long ctas = ((long)p.nvec + warps - 1) / warps;
+    const long cap = (long)sm_count() * MINB;
+    if (ctas > cap) ctas = cap;
+    kern<<<(unsigned)ctas, 128, smem, s>>>(p);
+    return (int)cudaGetLastError();
+}
+
+template <typename T, typename VT, int VARIANT, bool IEEE, bool TAIL>
+static int dispatch_h(const K2Params &p, cudaStream_t s) {
+    const int per_lane = ((p.H >> 2) + 31) / 32;
+    constexpr bool wide = sizeof(T) == 4;
+    if (per_lane <= 8) return launch_regs<T, VT, 8, VARIANT, IEEE, TAIL, wide ? 6 : 8>(p, s);
+    if (per_lane <= 16) return launch_regs<T, VT, 16, VARIANT, IEEE, TAIL, wide ? 4 : 6>(p, s);
+    if constexpr (!wide) {
+        if (per_lane <= 28) return launch_regs<T, VT, 28, VARIANT, IEEE, TAIL, 4>(p, s);
+        if (per_lane <= 32) return launch_regs<T, VT, 32, VARIANT, IEEE, TAIL, 4>(p, s);
+        if (per_lane <= 40) return launch_regs<T, VT, 40, VARIANT, IEEE, TAIL, 3>(p, s);
+        if (per_lane <= 64) return launch_regs<T, VT, 64, VARIANT, IEEE, TAIL, 2>(p, s);
+    }
+    if (TAIL) return IA_ERR_TOO_LARGE;
+    long ctas = ((long)p.nvec + 3) / 4;
+    const long cap = (long)sm_count() * 8;
+    if (ctas > cap) ctas = cap;
+    k2_twopass_kernel<T, VT, VARIANT, IEEE><<<(unsigned)ctas, 128, 0, s>>>(p);
+    return (int)cudaGetLastError();
+}
+
+template <typename T, typename VT, bool TAIL> static int dispatch_flags(const K2Params &p, int variant, int flags, cudaStream_t s) {
+    const bool ieee = (flags & IA_RSQRT_IEEE) != 0;
+    if (TAIL || variant == IA_NORM_GEMMA)
+        return ieee ? dispatch_h<T, VT, IA_NORM_GEMMA, true, TAIL>(p, s) : dispatch_h<T, VT, IA_NORM_GEMMA, false, TAIL>(p, s);
+    return ieee ? dispatch_h<T, VT, IA_NORM_LLAMA, true, false>(p, s) : dispatch_h<T, VT, IA_NORM_LLAMA, false, false>(p, s);
+}
+
+template <bool TAIL> static int dispatch_dtype(const K2Params &p, int dtype, int vec_dtype, int variant, int flags, cudaStream_t s) {
+    if (vec_dtype != dtype && vec_dtype != IA_F32) return IA_ERR_DTYPE;
+    switch (dtype) {
+    case IA_BF16:
+        return vec_dtype == IA_F32 ? dispatch_flags<__nv_bfloat16, float, TAIL>(p, variant, flags, s)
+                                   : dispatch_flags<__nv_bfloat16, __nv_bfloat16, TAIL>(p, variant, flags, s);
+    case IA_F16:
+        if (vec_dtype != IA_F16 || TAIL) return IA_ERR_DTYPE;  // fp16 models: table in fp16, no Gemma tail
+        return dispatch_flags<__half, __half, false>(p, variant, flags, s);
+    case IA_F32:
+        return dispatch_flags<float, float, TAIL>(p, variant, flags, s);
+    default:
+        return IA_ERR_DTYPE;
+    }
+}
+
+static int check_common(const void *h, const void *y, const void *vtable, const int32_t *row_vec,
+                        const float *row_alpha, const int32_t *row_t0, const void *w, int64_t rows,
+                        int64_t T, int64_t H, int32_t flags) {
+    if (!h || !y || !w) return IA_ERR_NULL;
+    if (row_vec && (!vtable || !row_alpha)) return IA_ERR_NULL;
+    if (row_vec && !(flags & IA_STEER_ALL) && !row_t0) return IA_ERR_NULL;
+    if (rows < 0 || T < 1 || H < 4 || H > 65536 || (H & 3)) return IA_ERR_SHAPE;
+    if (rows * T >= (int64_t)1 << 31) return IA_ERR_SHAPE;
+    if (!aligned16(h) || !aligned16(y) || !aligned16(w) || (vtable && !aligned16(vtable))) return IA_ERR_ALIGN;
+    return 0;
+}
+
+}  // namespace ia
+
+extern "C" int ia_inject_rmsnorm(void *h, void *y, const void *vtable, const int32_t *row_vec,
+                                 const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
+                                 int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype,
+                                 int32_t vec_dtype, int32_t variant, int32_t flags, void *stream) {
+    using namespace ia;
+    int rc = check_common(h, y, vtable, row_vec, row_alpha, row_t0, w, rows, T, H, flags);
+    if (rc) return rc;
+    if (variant != IA_NORM_LLAMA && variant != IA_NORM_GEMMA) return IA_ERR_DTYPE;
+    if (rows == 0) return 0;
+    K2Params p{};
+    p.h = h; p.y = y; p.mlp = nullptr; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
+    p.row_t0 = row_t0; p.w = w; p.w_post = nullptr; p.eps = eps; p.inv_h = 1.0f / (float)H;
+    p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
+    return dispatch_dtype<false>(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ia_gemma2_tail_inject_rmsnorm(const void *mlp_out, void *residual, void *y, const void *vtable,
+                                             const int32_t *row_vec, const float *row_alpha,
+                                             const int32_t *row_t0, const void *w_post, const void *w_next,
+                                             float eps, int64_t rows, int64_t T, int64_t H, int32_t pos0,
+                                             int32_t dtype, int32_t vec_dtype, int32_t flags, void *stream) {
+    using namespace ia;
+    if (!mlp_out || !w_post) return IA_ERR_NULL;
+    int rc = check_common(residual, y, vtable, row_vec, row_alpha, row_t0, w_next, rows, T, H, flags);
+    if (rc) return rc;
+    if (!aligned16(mlp_out) || !aligned16(w_post)) return IA_ERR_ALIGN;
+    if (rows == 0) return 0;
+    K2Params p{};
+    p.h = residual; p.y = y; p.mlp = mlp_out; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
+    p.row_t0 = row_t0; p.w = w_next; p.w_post = w_post; p.eps = eps; p.inv_h = 1.0f / (float)H;
+    p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
+    return dispatch_dtype<true>(p, dtype, vec_dtype, IA_NORM_GEMMA, flags, static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,521 @@
+// K1: fused residual gather + segmented fp32 mean-difference + L2 norm (sm_100a).
+//
+// A lane owns 8 consecutive columns (one 128-bit load of a 16-bit dtype, two of fp32); a warp
+// owns a 256-column tile of one layer.  Rows are gathered straight out of the residual-stream
+// tensors the forward pass produced (pointer table + row/token index), so the captured
+// activations never make a separate trip through HBM or the host.
+//
+// Numeric contract (include/ia_b200.h, oracle/kernels_np.py:meandiff):
+//   column sums: sequential over rows inside chunks of 256 rows, chunk sums added in order;
+//   mean = sum / n (IEEE division), rounded to the model dtype for the reference-rounded output;
+//   squared norms: per lane fmaf over its 8 columns left to right, xor-butterfly 16..1 across the
+//   warp, tiles added in ascending order by one thread.
+// HBM-bound streaming: algorithmic bytes per layer (n_concept + n_base)*H*e_in + n_out*H*e_out.
+
+#include <algorithm>
+
+#include "ia_common.cuh"
+
+namespace ia {
+
+constexpr int kChunkRows = 256;
+constexpr int kTileCols = 256;
+
+template <typename T> __device__ __forceinline__ void load8(const T *p, float (&f)[8]);
+template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16 *p, float (&f)[8]) {
+    const uint4 r = __ldg(reinterpret_cast<const uint4 *>(p));
+    f[0] = __uint_as_float(r.x << 16); f[1] = __uint_as_float(r.x & 0xffff0000u);
+    f[2] = __uint_as_float(r.y << 16); f[3] = __uint_as_float(r.y & 0xffff0000u);
+    f[4] = __uint_as_float(r.z << 16); f[5] = __uint_as_float(r.z & 0xffff0000u);
+    f[6] = __uint_as_float(r.w << 16); f[7] = __uint_as_float(r.w & 0xffff0000u);
+}
+template <> __device__ __forceinline__ void load8<__half>(const __half *p, float (&f)[8]) {
+    const uint4 r = __ldg(reinterpret_cast<const uint4 *>(p));
+    const __half2 *h = reinterpret_cast<const __half2 *>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { f[2 * i] = __low2float(h[i]); f[2 * i + 1] = __high2float(h[i]); }
+}
+template <> __device__ __forceinline__ void load8<float>(const float *p, float (&f)[8]) {
+    const float4 a = __ldg(reinterpret_cast<const float4 *>(p));
+    const float4 b = __ldg(reinterpret_cast<const float4 *>(p) + 1);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+// v[] must hold values representable in T.
+template <typename T> __device__ __forceinline__ void store8(T *p, const float (&v)[8]);
+template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16 *p, const float (&v)[8]) {
+    uint4 r;
+    r.x = (__float_as_uint(v[0]) >> 16) | (__float_as_uint(v[1]) & 0xffff0000u);
+    r.y = (__float_as_uint(v[2]) >> 16) | (__float_as_uint(v[3]) & 0xffff0000u);
+    r.z = (__float_as_uint(v[4]) >> 16) | (__float_as_uint(v[5]) & 0xffff0000u);
+    r.w = (__float_as_uint(v[6]) >> 16) | (__float_as_uint(v[7]) & 0xffff0000u);
+    *reinterpret_cast<uint4 *>(p) = r;
+}
+template <> __device__ __forceinline__ void store8<__half>(__half *p, const float (&v)[8]) {
+    uint4 r;
+    __half2 *h = reinterpret_cast<__half2 *>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __halves2half2(__float2half_rn(v[2 * i]), __float2half_rn(v[2 * i + 1]));
+    *reinterpret_cast<uint4 *>(p) = r;
+}
+template <> __device__ __forceinline__ void store8<float>(float *p, const float (&v)[8]) {
+    reinterpret_cast<float4 *>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4 *>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+__device__ __forceinline__ float sq8_warp(const float (&v)[8]) {
+    float a = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a = __fmaf_rn(v[i], v[i], a);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) a = __fadd_rn(a, __shfl_xor_sync(FULL, a, off));
+    return a;
+}
+
+// Where a segment's rows live: gathered from per-layer residual tensors, or compact.
+template <typename T> struct RowSource {
+    const void *const *ptrs;  // gathered: [n_layers] tensor base pointers; compact: nullptr
+    const T *compact;         // compact: [n_layers, n, H]
+    const int32_t *row;
+    const int32_t *tok;
+    int64_t T_len;
+    int64_t n;
+    __device__ __forceinline__ const T *at(int layer, int64_t r, int H) const {
+        if (ptrs) {
+            const T *base = static_cast<const T *>(ptrs[layer]);
+            const int64_t b = row ? row[r] : r;
+            const int64_t t = tok ? tok[r] : T_len - 1;
+            return base + (b * T_len + t) * (int64_t)H;
+        }
+        return compact + ((int64_t)layer * n + r) * (int64_t)H;
+    }
+};
+
+// Sequential fp32 sum of rows [r0, r1) of `src` for this lane's 8 columns; optionally copies
+// the rows to a compact buffer on the way.
+template <typename T>
+__device__ __forceinline__ void sum_rows(const RowSource<T> &src, int layer, int64_t r0, int64_t r1, int H, int col,
+                                         float (&acc)[8], T *copy_to /* [n, H] for this layer or null */) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    int64_t r = r0;
+    constexpr int U = 8;
+    for (; r + U <= r1; r += U) {
+        float f[U][8];
+#pragma unroll
+        for (int u = 0; u < U; ++u) load8<T>(src.at(layer, r + u, H) + col, f[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[u][i]);
+            if (copy_to) store8<T>(copy_to + (r + u) * (int64_t)H + col, f[u]);
+        }
+    }
+    for (; r < r1; ++r) {
+        float f[8];
+        load8<T>(src.at(layer, r, H) + col, f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+        if (copy_to) store8<T>(copy_to + r * (int64_t)H + col, f);
+    }
+}
+
+struct K1Out {
+    float *out_f32;     // [n_layers, n_out, H] or null
+    void *out_rounded;  // [n_layers, n_out, H]
+    float *part32;      // [n_layers, n_out, ntiles] squared-norm partials of out_f32
+    float *partr;       // [n_layers, n_out, ntiles] squared-norm partials of out_rounded
+    int ntiles;
+};
+
+// Concept rows [c0, c1) step cstep of one (layer, tile): difference against the mean, both
+// roundings, norm partials.
+template <typename T>
+__device__ __forceinline__ void emit_rows(const RowSource<T> &csrc, int layer, int tile, int lane, int H, int col,
+                                          bool active, bool raw, const float (&mean32)[8], const float (&meanr)[8],
+                                          int64_t c0, int64_t cstep, const K1Out &o) {
+    const int64_t n_out = csrc.n;
+    for (int64_t c = c0; c < n_out; c += cstep) {
+        float a[8], v32[8], vr[8];
+        if (active) {
+            load8<T>(csrc.at(layer, c, H) + col, a);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            v32[i] = raw ? a[i] : __fsub_rn(a[i], mean32[i]);
+            vr[i] = raw ? a[i] : Elt<T>::rd(__fsub_rn(a[i], meanr[i]));
+        }
+        const int64_t orow = (int64_t)layer * n_out + c;
+        if (active) {
+            if (o.out_f32) store8<float>(o.out_f32 + orow * H + col, v32);
+            store8<T>(static_cast<T *>(o.out_rounded) + orow * H + col, vr);
+        }
+        const float p32 = sq8_warp(v32);
+        const float pr = sq8_warp(vr);
+        if (lane == 0) {
+            o.part32[orow * o.ntiles + tile] = p32;
+            o.partr[orow * o.ntiles + tile] = pr;
+        }
+    }
+}
+
+// Fused path: n_base <= 256 (or RAW).  One warp per (layer, tile).
+template <typename T>
+__global__ void __launch_bounds__(128) k1_fused_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
+                                                       K1Out o) {
+    const int lane = threadIdx.x & 31;
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (w >= n_layers * o.ntiles) return;
+    const int layer = w / o.ntiles;
+    const int tile = w - layer * o.ntiles;
+    const int col = tile * kTileCols + lane * 8;
+    const bool active = col < H;
+    float mean32[8], meanr[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { mean32[i] = 0.f; meanr[i] = 0.f; }
+    if (!raw && active) {
+        float acc[8];
+        sum_rows<T>(bsrc, layer, 0, bsrc.n, H, col, acc, nullptr);
+        const float nb = (float)bsrc.n;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            mean32[i] = __fdiv_rn(acc[i], nb);
+            meanr[i] = Elt<T>::rd(mean32[i]);
+        }
+    }
+    emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, 0, 1, o);
+}
+
+// Chunked column sums: one warp per (chunk, layer, tile); also the rank-local gather.
+template <typename T>
+__global__ void __launch_bounds__(128) k1_segsum_kernel(RowSource<T> src, int n_layers, int H, int ntiles, int nchunks,
+                                                        float *part /* [nchunks, n_layers, H] */, T *copy_to) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (w >= (int64_t)nchunks * n_layers * ntiles) return;
+    const int tile = (int)(w % ntiles);
+    const int layer = (int)((w / ntiles) % n_layers);
+    const int chunk = (int)(w / ((int64_t)ntiles * n_layers));
+    const int col = tile * kTileCols + lane * 8;
+    if (col >= H) return;
+    const int64_t r0 = (int64_t)chunk * kChunkRows;
+    const int64_t r1 = r0 + kChunkRows < src.n ? r0 + kChunkRows : src.n;
+    float acc[8];
+    sum_rows<T>(src, layer, r0, r1, H, col, acc, copy_to ? copy_to + (int64_t)layer * src.n * H : nullptr);
+    store8<float>(part + ((int64_t)chunk * n_layers + layer) * H + col, acc);
+}
+
+// out[l, :] = part[0, l, :] + part[1, l, :] + ... in ascending chunk order.
+__global__ void k1_chunk_reduce_kernel(const float *part, float *out, int64_t per_chunk, int nchunks) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= per_chunk) return;
+    float s = part[i];
+    for (int c = 1; c < nchunks; ++c) s = __fadd_rn(s, part[(int64_t)c * per_chunk + i]);
+    out[i] = s;
+}
+
+// Finalize from given column sums.  grid.y splits the concept rows.
+template <typename T>
+__global__ void __launch_bounds__(128) k1_finalize_kernel(RowSource<T> csrc, const float *base_sum, float n_base,
+                                                          const float *pos_sum, float n_pos, int n_layers, int H, int mode,
+                                                          K1Out o) {
+    const int lane = threadIdx.x & 31;
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (w >= n_layers * o.ntiles) return;
+    const int layer = w / o.ntiles;
+    const int tile = w - layer * o.ntiles;
+    const int col = tile * kTileCols + lane * 8;
+    const bool active = col < H;
+    float mean32[8], meanr[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { mean32[i] = 0.f; meanr[i] = 0.f; }
+    if (mode != IA_MODE_RAW && active) {
+        float s[8];
+        load8<float>(base_sum + (int64_t)layer * H + col, s);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            mean32[i] = __fdiv_rn(s[i], n_base);
+            meanr[i] = Elt<T>::rd(mean32[i]);
+        }
+    }
+    if (mode == IA_MODE_POSNEG) {
+        if (blockIdx.y != 0) return;
+        float v32[8], vr[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { v32[i] = 0.f; vr[i] = 0.f; }
+        if (active) {
+            float s[8];
+            load8<float>(pos_sum + (int64_t)layer * H + col, s);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float p32 = __fdiv_rn(s[i], n_pos);
+                v32[i] = __fsub_rn(p32, mean32[i]);
+                vr[i] = Elt<T>::rd(__fsub_rn(Elt<T>::rd(p32), meanr[i]));
+            }
+            if (o.out_f32) store8<float>(o.out_f32 + (int64_t)layer * H + col, v32);
+            store8<T>(static_cast<T *>(o.out_rounded) + (int64_t)layer * H + col, vr);
+        }
+        const float p32 = sq8_warp(v32);
+        const float pr = sq8_warp(vr);
+        if (lane == 0) {
+            o.part32[(int64_t)layer * o.ntiles + tile] = p32;
+            o.partr[(int64_t)layer * o.ntiles + tile] = pr;
+        }
+        return;
+    }
+    emit_rows<T>(csrc, layer, tile, lane, H, col, active, mode == IA_MODE_RAW, mean32, meanr, blockIdx.y, gridDim.y, o);
+}
+
+// One warp per output row: tile partials -> norms; optional normalisation.
+template <typename T>
+__global__ void __launch_bounds__(128) k1_norm_kernel(int64_t n_rows, int H, int normalize, float *out_norm, K1Out o) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= n_rows) return;
+    float t32 = 0.f, tr = 0.f;
+    if (lane == 0) {
+        t32 = o.part32[row * o.ntiles];
+        tr = o.partr[row * o.ntiles];
+        for (int k = 1; k < o.ntiles; ++k) {
+            t32 = __fadd_rn(t32, o.part32[row * o.ntiles + k]);
+            tr = __fadd_rn(tr, o.partr[row * o.ntiles + k]);
+        }
+    }
+    t32 = __shfl_sync(FULL, t32, 0);
+    tr = __shfl_sync(FULL, tr, 0);
+    const float norm32 = __fsqrt_rn(t32);
+    const float normr = Elt<T>::rd(__fsqrt_rn(tr));
+    if (lane == 0 && out_norm) out_norm[row] = normr;
+    if (!normalize) return;
+    const float den32 = __fadd_rn(norm32, 1e-8f);
+    const float denr = Elt<T>::rd(__fadd_rn(normr, 1e-8f));
+    T *vr = static_cast<T *>(o.out_rounded) + row * H;
+    for (int col = lane * 8; col < H; col += 256) {
+        float f[8];
+        // plain loads: this kernel writes the same buffer
+        Pack4<T> a = ld4<T>(vr + col), b = ld4<T>(vr + col + 4);
+        float fa[4], fb[4];
+        Elt<T>::unpack(a, fa); Elt<T>::unpack(b, fb);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { f[i] = Elt<T>::rd(__fdiv_rn(fa[i], denr)); f[4 + i] = Elt<T>::rd(__fdiv_rn(fb[i], denr)); }
+        store8<T>(vr + col, f);
+        if (o.out_f32) {
+            float *v = o.out_f32 + row * H + col;
+            float4 x = reinterpret_cast<float4 *>(v)[0], y = reinterpret_cast<float4 *>(v)[1];
+            x.x = __fdiv_rn(x.x, den32); x.y = __fdiv_rn(x.y, den32); x.z = __fdiv_rn(x.z, den32); x.w = __fdiv_rn(x.w, den32);
+            y.x = __fdiv_rn(y.x, den32); y.y = __fdiv_rn(y.y, den32); y.z = __fdiv_rn(y.z, den32); y.w = __fdiv_rn(y.w, den32);
+            reinterpret_cast<float4 *>(v)[0] = x; reinterpret_cast<float4 *>(v)[1] = y;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+
+static inline int64_t up64(int64_t x) { return (x + 63) / 64 * 64; }  // floats -> 256-byte multiples
+static inline int nchunks_of(int64_t n) { return (int)((n + kChunkRows - 1) / kChunkRows); }
+
+struct WsLayout {
+    int64_t part32, partr, base_part, base_sum, pos_part, pos_sum, total;  // offsets in floats
+};
+
+static WsLayout ws_layout(int64_t L, int64_t n_concept, int64_t n_base, int64_t H, int mode) {
+    const int64_t ntiles = (H + kTileCols - 1) / kTileCols;
+    const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : n_concept;
+    WsLayout w{};
+    int64_t off = 0;
+    w.part32 = off; off += up64(L * n_out * ntiles);
+    w.partr = off; off += up64(L * n_out * ntiles);
+    w.base_part = off; off += up64((int64_t)nchunks_of(n_base) * L * H);
+    w.base_sum = off; off += up64(L * H);
+    w.pos_part = off; off += mode == IA_MODE_POSNEG ? up64((int64_t)nchunks_of(n_concept) * L * H) : 0;
+    w.pos_sum = off; off += mode == IA_MODE_POSNEG ? up64(L * H) : 0;
+    w.total = off;
+    return w;
+}
+
+template <typename T>
+static int run_segsum(const RowSource<T> &src, int L, int H, float *part, float *sum_out, T *copy_to, cudaStream_t s) {
+    const int ntiles = (H + kTileCols - 1) / kTileCols;
+    const int nch = nchunks_of(src.n);
+    if (src.n == 0) return (int)cudaMemsetAsync(sum_out, 0, sizeof(float) * (size_t)L * H, s);
+    const int64_t warps = (int64_t)nch * L * ntiles;
+    float *dst = nch == 1 ? sum_out : part;
+    k1_segsum_kernel<T><<<(unsigned)((warps + 3) / 4), 128, 0, s>>>(src, L, H, ntiles, nch, dst, copy_to);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    if (nch > 1) {
+        const int64_t per = (int64_t)L * H;
+        k1_chunk_reduce_kernel<<<(unsigned)((per + 255) / 256), 256, 0, s>>>(part, sum_out, per, nch);
+        e = cudaGetLastError();
+    }
+    return (int)e;
+}
+
+template <typename T>
+static int run_finalize(const RowSource<T> &csrc, const float *base_sum, int64_t n_base, const float *pos_sum,
+                        int64_t n_pos, int L, int H, int mode, int normalize, float *out_norm, K1Out o, cudaStream_t s) {
+    const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : csrc.n;
+    const int warps = L * o.ntiles;
+    int split = 1;
+    if (mode != IA_MODE_POSNEG) {
+        // enough warps to fill the machine: ~8 per SM
+        split = (int)std::min<int64_t>(std::max<int64_t>(1, (148 * 8 + warps - 1) / warps), std::max<int64_t>(1, n_out));
+    }
+    dim3 grid((unsigned)((warps + 3) / 4), (unsigned)split);
+    k1_finalize_kernel<T><<<grid, 128, 0, s>>>(csrc, base_sum, (float)n_base, pos_sum, (float)n_pos, L, H, mode, o);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    const int64_t rows = (int64_t)L * n_out;
+    k1_norm_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(rows, H, normalize, out_norm, o);
+    return (int)cudaGetLastError();
+}
+
+template <typename T>
+static int gather_meandiff_t(const void *const *cptrs, int64_t Tc, const int32_t *crow, const int32_t *ctok, int64_t nc,
+                             const void *const *bptrs, int64_t Tb, const int32_t *brow, const int32_t *btok, int64_t nb,
+                             int L, int H, int mode, int normalize, float *out_f32, void *out_rounded, float *out_norm,
+                             float *ws, cudaStream_t s) {
+    const WsLayout wl = ws_layout(L, nc, nb, H, mode);
+    const int ntiles = (H + kTileCols - 1) / kTileCols;
+    RowSource<T> csrc{cptrs, nullptr, crow, ctok, Tc, nc};
+    RowSource<T> bsrc{bptrs, nullptr, brow, btok, Tb, nb};
+    K1Out o{out_f32, out_rounded, ws + wl.part32, ws + wl.partr, ntiles};
+    const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : nc;
+    if (mode != IA_MODE_POSNEG && (mode == IA_MODE_RAW || nb <= kChunkRows)) {
+        const int warps = L * ntiles;
+        k1_fused_kernel<T><<<(unsigned)((warps + 3) / 4), 128, 0, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, o);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return (int)e;
+        const int64_t rows = (int64_t)L * n_out;
+        k1_norm_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(rows, H, normalize, out_norm, o);
+        return (int)cudaGetLastError();
+    }
+    int rc = run_segsum<T>(bsrc, L, H, ws + wl.base_part, ws + wl.base_sum, nullptr, s);
+    if (rc) return rc;
+    if (mode == IA_MODE_POSNEG) {
+        rc = run_segsum<T>(csrc, L, H, ws + wl.pos_part, ws + wl.pos_sum, nullptr, s);
+        if (rc) return rc;
+    }
+    return run_finalize<T>(csrc, ws + wl.base_sum, nb, ws + wl.pos_sum, nc, L, H, mode, normalize, out_norm, o, s);
+}
+
+static int check_sizes(int64_t L, int64_t H, int64_t n) {
+    if (L < 1 || L > 4096 || H < 8 || H > 65536 || (H & 7) || n < 0 || n > ((int64_t)1 << 30)) return IA_ERR_SHAPE;
+    return 0;
+}
+
+}  // namespace ia
+
+extern "C" int64_t ia_meandiff_workspace_bytes(int64_t n_layers, int64_t n_concept, int64_t n_base, int64_t H, int32_t mode) {
+    if (ia::check_sizes(n_layers, H, n_concept) || n_base < 0) return IA_ERR_SHAPE;
+    return ia::ws_layout(n_layers, n_concept, n_base, H, mode).total * (int64_t)sizeof(float);
+}
+
+extern "C" int ia_gather_meandiff(const void *const *concept_ptrs, int64_t Tc, const int32_t *concept_row,
+                                  const int32_t *concept_tok, int64_t n_concept, const void *const *base_ptrs,
+                                  int64_t Tb, const int32_t *base_row, const int32_t *base_tok, int64_t n_base,
+                                  int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,
+                                  void *out_rounded, float *out_norm, void *workspace, int64_t workspace_bytes,
+                                  int32_t dtype, void *stream) {
+    using namespace ia;
+    if (mode < IA_MODE_BASELINE || mode > IA_MODE_POSNEG) return IA_ERR_DTYPE;
+    if (!concept_ptrs || !out_rounded || !workspace) return IA_ERR_NULL;
+    if (mode != IA_MODE_RAW && !base_ptrs) return IA_ERR_NULL;
+    int rc = check_sizes(n_layers, H, n_concept);
+    if (rc) return rc;
+    if (Tc < 1 || (mode != IA_MODE_RAW && (Tb < 1 || n_base < 1)) || n_base < 0) return IA_ERR_SHAPE;
+    if (!aligned16(out_rounded) || !aligned16(workspace) || (out_f32 && !aligned16(out_f32))) return IA_ERR_ALIGN;
+    if (mode == IA_MODE_RAW) n_base = 0;
+    if (workspace_bytes < ia_meandiff_workspace_bytes(n_layers, n_concept, n_base, H, mode)) return IA_ERR_WORKSPACE;
+    if (n_concept == 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    float *ws = static_cast<float *>(workspace);
+    switch (dtype) {
+    case IA_BF16:
+        return gather_meandiff_t<__nv_bfloat16>(concept_ptrs, Tc, concept_row, concept_tok, n_concept, base_ptrs, Tb, base_row,
+                                                base_tok, n_base, (int)n_layers, (int)H, mode, normalize, out_f32, out_rounded,
+                                                out_norm, ws, s);
+    case IA_F16:
+        return gather_meandiff_t<__half>(concept_ptrs, Tc, concept_row, concept_tok, n_concept, base_ptrs, Tb, base_row, base_tok,
+                                         n_base, (int)n_layers, (int)H, mode, normalize, out_f32, out_rounded, out_norm, ws, s);
+    case IA_F32:
+        return gather_meandiff_t<float>(concept_ptrs, Tc, concept_row, concept_tok, n_concept, base_ptrs, Tb, base_row, base_tok,
+                                        n_base, (int)n_layers, (int)H, mode, normalize, out_f32, out_rounded, out_norm, ws, s);
+    default:
+        return IA_ERR_DTYPE;
+    }
+}
+
+extern "C" int ia_gather_segsum(const void *const *layer_ptrs, int64_t T, const int32_t *row_idx, const int32_t *tok_idx,
+                                int64_t n_rows, int64_t n_layers, int64_t H, void *out_rows, float *out_sum, void *workspace,
+                                int64_t workspace_bytes, int32_t dtype, void *stream) {
+    using namespace ia;
+    if (!layer_ptrs || !out_sum || !workspace) return IA_ERR_NULL;
+    int rc = check_sizes(n_layers, H, n_rows);
+    if (rc) return rc;
+    if (T < 1) return IA_ERR_SHAPE;
+    if (!aligned16(out_sum) || !aligned16(workspace) || (out_rows && !aligned16(out_rows))) return IA_ERR_ALIGN;
+    if (workspace_bytes < ia_meandiff_workspace_bytes(n_layers, 0, n_rows, H, IA_MODE_BASELINE)) return IA_ERR_WORKSPACE;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const WsLayout wl = ws_layout(n_layers, 0, n_rows, H, IA_MODE_BASELINE);
+    float *part = static_cast<float *>(workspace) + wl.base_part;
+    switch (dtype) {
+    case IA_BF16: {
+        RowSource<__nv_bfloat16> src{layer_ptrs, nullptr, row_idx, tok_idx, T, n_rows};
+        return run_segsum<__nv_bfloat16>(src, (int)n_layers, (int)H, part, out_sum, static_cast<__nv_bfloat16 *>(out_rows), s);
+    }
+    case IA_F16: {
+        RowSource<__half> src{layer_ptrs, nullptr, row_idx, tok_idx, T, n_rows};
+        return run_segsum<__half>(src, (int)n_layers, (int)H, part, out_sum, static_cast<__half *>(out_rows), s);
+    }
+    case IA_F32: {
+        RowSource<float> src{layer_ptrs, nullptr, row_idx, tok_idx, T, n_rows};
+        return run_segsum<float>(src, (int)n_layers, (int)H, part, out_sum, static_cast<float *>(out_rows), s);
+    }
+    default:
+        return IA_ERR_DTYPE;
+    }
+}
+
+extern "C" int ia_meandiff_finalize(const void *concept_acts, int64_t n_concept, const float *base_sum, int64_t n_base_total,
+                                    int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,
+                                    void *out_rounded, float *out_norm, void *workspace, int64_t workspace_bytes,
+                                    int32_t dtype, void *stream) {
+    using namespace ia;
+    if (mode < IA_MODE_BASELINE || mode > IA_MODE_RAW) return IA_ERR_DTYPE;  // POSNEG needs both sums: use ia_gather_meandiff
+    if (!concept_acts || !out_rounded || !workspace) return IA_ERR_NULL;
+    if (mode != IA_MODE_RAW && (!base_sum || n_base_total < 1)) return IA_ERR_NULL;
+    int rc = check_sizes(n_layers, H, n_concept);
+    if (rc) return rc;
+    if (!aligned16(concept_acts) || !aligned16(out_rounded) || !aligned16(workspace) || (out_f32 && !aligned16(out_f32)) ||
+        (base_sum && !aligned16(base_sum)))
+        return IA_ERR_ALIGN;
+    if (workspace_bytes < ia_meandiff_workspace_bytes(n_layers, n_concept, 0, H, mode)) return IA_ERR_WORKSPACE;
+    if (n_concept == 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const WsLayout wl = ws_layout(n_layers, n_concept, 0, H, mode);
+    float *ws = static_cast<float *>(workspace);
+    const int ntiles = (int)((H + kTileCols - 1) / kTileCols);
+    K1Out o{out_f32, out_rounded, ws + wl.part32, ws + wl.partr, ntiles};
+    switch (dtype) {
+    case IA_BF16: {
+        RowSource<__nv_bfloat16> c{nullptr, static_cast<const __nv_bfloat16 *>(concept_acts), nullptr, nullptr, 1, n_concept};
+        return run_finalize<__nv_bfloat16>(c, base_sum, n_base_total, nullptr, 1, (int)n_layers, (int)H, mode, normalize, out_norm, o, s);
+    }
+    case IA_F16: {
+        RowSource<__half> c{nullptr, static_cast<const __half *>(concept_acts), nullptr, nullptr, 1, n_concept};
+        return run_finalize<__half>(c, base_sum, n_base_total, nullptr, 1, (int)n_layers, (int)H, mode, normalize, out_norm, o, s);
+    }
+    case IA_F32: {
+        RowSource<float> c{nullptr, static_cast<const float *>(concept_acts), nullptr, nullptr, 1, n_concept};
+        return run_finalize<float>(c, base_sum, n_base_total, nullptr, 1, (int)n_layers, (int)H, mode, normalize, out_norm, o, s);
+    }
+    default:
+        return IA_ERR_DTYPE;
+    }
+}

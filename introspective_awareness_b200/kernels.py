@@ -1,0 +1,190 @@
+"""Torch-tensor front end of the C ABI: validates tensors, passes raw pointers + the current
+CUDA stream.  PyTorch only owns the memory and the stream here; all arithmetic is in
+libia_b200.so.  Every function raises if the inputs are not CUDA tensors — there is no CPU path.
+"""
+
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import (IA_BF16, IA_F16, IA_F32, IA_IMPL_TMA, IA_MODE_BASELINE, IA_MODE_POSNEG, IA_MODE_RAW,
+                   IA_MODE_SIMPLE, IA_NORM_GEMMA, IA_NORM_LLAMA, IA_RSQRT_IEEE, IA_STEER_ALL, check)
+
+_DTYPES = {torch.bfloat16: IA_BF16, torch.float16: IA_F16, torch.float32: IA_F32}
+MODES = {"baseline": IA_MODE_BASELINE, "simple": IA_MODE_SIMPLE, "no_baseline": IA_MODE_RAW, "raw": IA_MODE_RAW,
+         "posneg": IA_MODE_POSNEG}
+VARIANTS = {"llama": IA_NORM_LLAMA, "qwen2": IA_NORM_LLAMA, "gemma": IA_NORM_GEMMA, "gemma2": IA_NORM_GEMMA}
+
+
+def _dt(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype}") from None
+
+
+def _cuda(t: Optional[torch.Tensor], name: str, dtype=None) -> int:
+    if t is None:
+        return 0
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: the steering/extraction kernels have no CPU path")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: str,
+                   vtable: Optional[torch.Tensor] = None, row_vec: Optional[torch.Tensor] = None,
+                   row_alpha: Optional[torch.Tensor] = None, row_t0: Optional[torch.Tensor] = None,
+                   pos0: int = 0, steer_all: bool = False, out: Optional[torch.Tensor] = None,
+                   ieee_rsqrt: bool = False, impl: str = "regs") -> torch.Tensor:
+    """K2.  `h` [rows, T, H] is updated in place with the per-row injection; returns y = RMSNorm(h').
+    With row_vec None this is a plain RMSNorm of `variant`."""
+    if h.dim() != 3:
+        raise ValueError("h must be [rows, T, H]")
+    rows, t_len, hid = h.shape
+    y = torch.empty_like(h) if out is None else out
+    flags = (IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0) | (IA_IMPL_TMA if impl == "tma" else 0)
+    lib = _lib.load()
+    rc = lib.ia_inject_rmsnorm(
+        _cuda(h, "h"), _cuda(y, "out", h.dtype), _cuda(vtable, "vtable"), _cuda(row_vec, "row_vec", torch.int32),
+        _cuda(row_alpha, "row_alpha", torch.float32), _cuda(row_t0, "row_t0", torch.int32),
+        _cuda(weight, "weight", h.dtype), float(eps), rows, t_len, hid, int(pos0), _dt(h),
+        _dt(vtable) if vtable is not None else _dt(h), VARIANTS[variant], flags, _stream())
+    check(rc, "ia_inject_rmsnorm")
+    return y
+
+
+def gemma2_tail_inject_rmsnorm(mlp_out: torch.Tensor, residual: torch.Tensor, w_post: torch.Tensor,
+                               w_next: torch.Tensor, eps: float, vtable=None, row_vec=None, row_alpha=None,
+                               row_t0=None, pos0: int = 0, steer_all: bool = False,
+                               out: Optional[torch.Tensor] = None, ieee_rsqrt: bool = False) -> torch.Tensor:
+    """K2 Gemma-2 block tail: residual <- inject(residual + gemma_norm(mlp_out; w_post)), returns
+    gemma_norm(residual; w_next)."""
+    rows, t_len, hid = residual.shape
+    y = torch.empty_like(residual) if out is None else out
+    flags = (IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
+    lib = _lib.load()
+    rc = lib.ia_gemma2_tail_inject_rmsnorm(
+        _cuda(mlp_out, "mlp_out", residual.dtype), _cuda(residual, "residual"), _cuda(y, "out", residual.dtype),
+        _cuda(vtable, "vtable"), _cuda(row_vec, "row_vec", torch.int32), _cuda(row_alpha, "row_alpha", torch.float32),
+        _cuda(row_t0, "row_t0", torch.int32), _cuda(w_post, "w_post", residual.dtype),
+        _cuda(w_next, "w_next", residual.dtype), float(eps), rows, t_len, hid, int(pos0), _dt(residual),
+        _dt(vtable) if vtable is not None else _dt(residual), flags, _stream())
+    check(rc, "ia_gemma2_tail_inject_rmsnorm")
+    return y
+
+
+def _ptr_table(tensors: Sequence[torch.Tensor], name: str) -> torch.Tensor:
+    ptrs = [_cuda(t, name) for t in tensors]
+    return torch.tensor(ptrs, dtype=torch.int64).to(tensors[0].device, non_blocking=False)
+
+
+def _idx(x, device) -> Optional[torch.Tensor]:
+    if x is None:
+        return None
+    if isinstance(x, torch.Tensor):
+        return x.to(device=device, dtype=torch.int32).contiguous()
+    return torch.tensor(list(x), dtype=torch.int32, device=device)
+
+
+def workspace_bytes(n_layers: int, n_concept: int, n_base: int, hidden: int, mode: str = "baseline") -> int:
+    n = _lib.load().ia_meandiff_workspace_bytes(n_layers, n_concept, n_base, hidden, MODES[mode])
+    if n < 0:
+        check(int(n), "ia_meandiff_workspace_bytes")
+    return int(n)
+
+
+def gather_meandiff(concept_layers: Sequence[torch.Tensor], base_layers: Optional[Sequence[torch.Tensor]],
+                    mode: str = "baseline", normalize: bool = False, concept_rows=None, concept_tok=None,
+                    base_rows=None, base_tok=None, n_concept: Optional[int] = None, n_base: Optional[int] = None,
+                    want_f32: bool = True, workspace: Optional[torch.Tensor] = None
+                    ) -> Tuple[Optional[torch.Tensor], torch.Tensor, torch.Tensor]:
+    """K1.  concept_layers / base_layers: one [B, T, H] residual tensor per selected layer.
+    Returns (v_f32 [L, n_out, H] or None, v_rounded [L, n_out, H] model dtype, norm [L, n_out])."""
+    first = concept_layers[0]
+    dev, dtype = first.device, first.dtype
+    n_layers, hid = len(concept_layers), first.shape[-1]
+    tc = first.shape[1]
+    n_concept = first.shape[0] if n_concept is None else n_concept
+    if concept_rows is not None:
+        n_concept = len(concept_rows)
+    imode = MODES[mode]
+    if imode == IA_MODE_RAW:
+        base_layers, n_base, tb = None, 0, 1
+    else:
+        if base_layers is None or len(base_layers) != n_layers:
+            raise ValueError("base_layers must have one tensor per layer")
+        tb = base_layers[0].shape[1]
+        n_base = base_layers[0].shape[0] if n_base is None else n_base
+        if base_rows is not None:
+            n_base = len(base_rows)
+    n_out = 1 if imode == IA_MODE_POSNEG else n_concept
+    out_f32 = torch.empty((n_layers, n_out, hid), dtype=torch.float32, device=dev) if want_f32 else None
+    out_r = torch.empty((n_layers, n_out, hid), dtype=dtype, device=dev)
+    out_n = torch.empty((n_layers, n_out), dtype=torch.float32, device=dev)
+    need = workspace_bytes(n_layers, n_concept, n_base, hid, mode)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+    cptr = _ptr_table(concept_layers, "concept_layers")
+    bptr = _ptr_table(base_layers, "base_layers") if base_layers is not None else None
+    crow, ctok = _idx(concept_rows, dev), _idx(concept_tok, dev)
+    brow, btok = _idx(base_rows, dev), _idx(base_tok, dev)
+    lib = _lib.load()
+    rc = lib.ia_gather_meandiff(
+        cptr.data_ptr(), tc, _cuda(crow, "concept_rows"), _cuda(ctok, "concept_tok"), n_concept,
+        bptr.data_ptr() if bptr is not None else 0, tb, _cuda(brow, "base_rows"), _cuda(btok, "base_tok"), n_base,
+        n_layers, hid, imode, int(bool(normalize)), _cuda(out_f32, "out_f32"), out_r.data_ptr(), out_n.data_ptr(),
+        workspace.data_ptr(), workspace.numel() * workspace.element_size(), _dt(first), _stream())
+    check(rc, "ia_gather_meandiff")
+    # keep index/pointer tensors alive until the launch is enqueued (it is, the call is synchronous on the host)
+    return out_f32, out_r, out_n
+
+
+def gather_segsum(layers: Sequence[torch.Tensor], rows=None, tok=None, n_rows: Optional[int] = None,
+                  want_rows: bool = True) -> Tuple[Optional[torch.Tensor], torch.Tensor]:
+    """K1a (rank-local): returns (rows [L, n, H] model dtype or None, column sums [L, H] fp32)."""
+    first = layers[0]
+    dev, hid, n_layers = first.device, first.shape[-1], len(layers)
+    n_rows = first.shape[0] if n_rows is None else n_rows
+    if rows is not None:
+        n_rows = len(rows)
+    out_rows = torch.empty((n_layers, n_rows, hid), dtype=first.dtype, device=dev) if want_rows else None
+    out_sum = torch.empty((n_layers, hid), dtype=torch.float32, device=dev)
+    need = workspace_bytes(n_layers, 0, n_rows, hid, "baseline")
+    ws = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+    ptrs = _ptr_table(layers, "layers")
+    ridx, tidx = _idx(rows, dev), _idx(tok, dev)
+    rc = _lib.load().ia_gather_segsum(ptrs.data_ptr(), first.shape[1], _cuda(ridx, "rows"), _cuda(tidx, "tok"), n_rows,
+                                      n_layers, hid, _cuda(out_rows, "out_rows"), out_sum.data_ptr(), ws.data_ptr(),
+                                      ws.numel(), _dt(first), _stream())
+    check(rc, "ia_gather_segsum")
+    return out_rows, out_sum
+
+
+def meandiff_finalize(concept_acts: torch.Tensor, base_sum: Optional[torch.Tensor], n_base_total: int,
+                      mode: str = "baseline", normalize: bool = False, want_f32: bool = True
+                      ) -> Tuple[Optional[torch.Tensor], torch.Tensor, torch.Tensor]:
+    """K1b: concept_acts [L, C, H] (model dtype) and all-reduced base_sum [L, H] fp32."""
+    n_layers, n_concept, hid = concept_acts.shape
+    dev = concept_acts.device
+    out_f32 = torch.empty((n_layers, n_concept, hid), dtype=torch.float32, device=dev) if want_f32 else None
+    out_r = torch.empty_like(concept_acts)
+    out_n = torch.empty((n_layers, n_concept), dtype=torch.float32, device=dev)
+    need = workspace_bytes(n_layers, n_concept, 0, hid, mode)
+    ws = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+    rc = _lib.load().ia_meandiff_finalize(
+        _cuda(concept_acts, "concept_acts"), n_concept, _cuda(base_sum, "base_sum", torch.float32), int(n_base_total),
+        n_layers, hid, MODES[mode], int(bool(normalize)), _cuda(out_f32, "out_f32"), out_r.data_ptr(),
+        out_n.data_ptr(), ws.data_ptr(), ws.numel(), _dt(concept_acts), _stream())
+    check(rc, "ia_meandiff_finalize")
+    return out_f32, out_r, out_n

@@ -1,0 +1,115 @@
+"""Kernel micro-benchmarks: K2 / K1 achieved HBM GB/s over the SURVEY.md §8(d) shape ladder.
+
+CUDA-event timing on the launching stream, >= 3 warm-ups, L2 flushed between timed launches for
+shapes smaller than L2 (a 256 MB write), one JSON line per shape.  Run on the B200 box:
+    python tools/kbench.py [--quick] [--impl regs|tma] > gpurun_out/kbench.jsonl
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from introspective_awareness_b200 import kernels  # noqa: E402
+
+PEAK_FALLBACK = 6650.0
+
+
+def peak_gbs():
+    p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    except Exception:
+        return PEAK_FALLBACK, "fallback"
+
+
+def time_launch(fn, reps, flush):
+    """Average device time (ms) of fn() over reps launches, each preceded by an L2 flush when asked."""
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    total = 0.0
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for a, b in ev:
+        if flush is not None:
+            flush.zero_()
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    for a, b in ev:
+        total += a.elapsed_time(b)
+    return total / reps
+
+
+def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16):
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(0)
+    h = torch.randn(rows, T, H, device=dev, generator=g).to(dtype)
+    y = torch.empty_like(h)
+    vt = (torch.randn(50, H, device=dev, generator=g) * 0.1).to(dtype)
+    w = torch.ones(H, device=dev, dtype=dtype)
+    row_vec = (torch.arange(rows, device=dev) % 50).to(torch.int32)
+    alpha = torch.full((rows,), 4.0, device=dev)
+    t0 = torch.zeros(rows, device=dev, dtype=torch.int32)
+    e = h.element_size()
+
+    def fn():
+        kernels.inject_rmsnorm(h, w, 1e-5, variant, vtable=vt, row_vec=row_vec, row_alpha=alpha, row_t0=t0,
+                               steer_all=True, out=y, impl=impl)
+
+    ms = time_launch(fn, reps, flush)
+    algo = rows * T * H * e * 4 + H * e
+    return dict(kernel="k2_inject_rmsnorm", impl=impl, variant=variant, rows=rows, T=T, H=H, bytes=algo,
+                us=ms * 1e3, gbs=algo / ms / 1e6)
+
+
+def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16):
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(0)
+    T = 1
+    cl = [torch.randn(C, T, H, device=dev, generator=g).to(dtype) for _ in range(n_layers)]
+    bl = [torch.randn(Nb, T, H, device=dev, generator=g).to(dtype) for _ in range(n_layers)]
+    e = cl[0].element_size()
+    ws = torch.empty(kernels.workspace_bytes(n_layers, C, Nb, H) + 256, dtype=torch.uint8, device=dev)
+
+    def fn():
+        kernels.gather_meandiff(cl, bl, "baseline", False, want_f32=False, workspace=ws)
+
+    ms = time_launch(fn, reps, flush)
+    algo = n_layers * ((C + Nb) * H * e + C * H * e)
+    return dict(kernel="k1_gather_meandiff", n_layers=n_layers, C=C, Nb=Nb, H=H, bytes=algo, us=ms * 1e3,
+                gbs=algo / ms / 1e6)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--impl", default="regs")
+    ap.add_argument("--reps", type=int, default=20)
+    args = ap.parse_args()
+    peak, src = peak_gbs()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda:0")
+    rows_ladder = [200, 3000, 25600] if args.quick else [200, 3000, 25600, 262144]
+    hs = [4096] if args.quick else [896, 3584, 4096, 5120]
+    for H in hs:
+        for rows in rows_ladder:
+            if rows * H * 2 * 2 > 40e9:
+                continue
+            r = bench_k2(rows, 1, H, "gemma" if H == 3584 else "llama", args.impl, args.reps, flush)
+            r.update(frac=r["gbs"] / peak, peak=peak, peak_src=src)
+            print(json.dumps(r), flush=True)
+    for (L, C, Nb) in ([(32, 50, 100)] if args.quick else [(1, 50, 100), (32, 50, 100), (1, 50, 16334), (1, 50, 262094)]):
+        r = bench_k1(L, C, Nb, 4096, args.reps, flush)
+        r.update(frac=r["gbs"] / peak, peak=peak, peak_src=src)
+        print(json.dumps(r), flush=True)
+
+
+if __name__ == "__main__":
+    main()
