@@ -35,6 +35,15 @@ template <> struct Elt<__nv_bfloat16> {
         p.raw.x = (__float_as_uint(f[0]) >> 16) | (__float_as_uint(f[1]) & 0xffff0000u);
         p.raw.y = (__float_as_uint(f[2]) >> 16) | (__float_as_uint(f[3]) & 0xffff0000u);
     }
+    // Round four floats to bf16 (RNE) with the packed two-at-a-time conversion (F2FP, ALU pipe)
+    // instead of four scalar F2F; leaves the rounded values widened in f[] and packed in p.
+    __device__ static __forceinline__ void rd4(float (&f)[4], Pack4<type> &p) {
+        __nv_bfloat162 a = __floats2bfloat162_rn(f[0], f[1]);
+        __nv_bfloat162 b = __floats2bfloat162_rn(f[2], f[3]);
+        p.raw.x = *reinterpret_cast<unsigned *>(&a);
+        p.raw.y = *reinterpret_cast<unsigned *>(&b);
+        unpack(p, f);
+    }
 };
 
 template <> struct Elt<__half> {
@@ -48,10 +57,14 @@ template <> struct Elt<__half> {
         f[2] = __low2float(b); f[3] = __high2float(b);
     }
     __device__ static __forceinline__ void pack_exact(const float (&f)[4], Pack4<type> &p) {
-        __half2 a = __halves2half2(__float2half_rn(f[0]), __float2half_rn(f[1]));
-        __half2 b = __halves2half2(__float2half_rn(f[2]), __float2half_rn(f[3]));
+        __half2 a = __floats2half2_rn(f[0], f[1]);
+        __half2 b = __floats2half2_rn(f[2], f[3]);
         p.raw.x = *reinterpret_cast<unsigned *>(&a);
         p.raw.y = *reinterpret_cast<unsigned *>(&b);
+    }
+    __device__ static __forceinline__ void rd4(float (&f)[4], Pack4<type> &p) {
+        pack_exact(f, p);
+        unpack(p, f);
     }
 };
 
@@ -65,6 +78,7 @@ template <> struct Elt<float> {
     __device__ static __forceinline__ void pack_exact(const float (&f)[4], Pack4<type> &p) {
         p.raw = make_float4(f[0], f[1], f[2], f[3]);
     }
+    __device__ static __forceinline__ void rd4(float (&f)[4], Pack4<type> &p) { pack_exact(f, p); }
 };
 
 template <typename T> __device__ __forceinline__ Pack4<T> ld4(const T *p) {

@@ -57,135 +57,175 @@ template <typename T, int VARIANT> __device__ __forceinline__ float norm_out(flo
     return Elt<T>::rd(__fmul_rn(n, __fadd_rn(1.0f, w)));
 }
 
-// Register-resident implementation: MAXJ = groups of 4 elements per lane (H <= 128 * MAXJ).
+// cp.async (LDGSTS) of one 4-element group: asynchronous, no register staging.
+template <int BYTES> __device__ __forceinline__ void cp_async_group(void *smem_dst, const void *gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;\n" ::"r"(d), "l"(gsrc), "n"(BYTES));
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n" ::);
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+template <typename T>
+__device__ __forceinline__ void sumsq4(const Pack4<T> &x, float &a0, float &a1, float &a2, float &a3) {
+    float f[4];
+    Elt<T>::unpack(x, f);
+    a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
+    a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
+    a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
+    a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
+}
+
+// y group = norm(x group): LLAMA rounds x*r to the dtype before the weight multiply.
+template <typename T, int VARIANT>
+__device__ __forceinline__ void norm4(const Pack4<T> &x, float r, const Pack4<T> &w, Pack4<T> &out) {
+    float f[4], wf[4];
+    Elt<T>::unpack(x, f);
+    Elt<T>::unpack(w, wf);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) f[i] = __fmul_rn(f[i], r);
+    if (VARIANT == IA_NORM_LLAMA) {
+        Pack4<T> tmp;
+        Elt<T>::rd4(f, tmp);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) f[i] = __fmul_rn(wf[i], f[i]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) f[i] = __fmul_rn(f[i], __fadd_rn(1.0f, wf[i]));
+    }
+    Elt<T>::rd4(f, out);
+}
+
+// x group += round(v group * alpha), rounded to the dtype.
+template <typename T, typename VT>
+__device__ __forceinline__ void inject4(Pack4<T> &x, const Pack4<VT> &v, float alpha) {
+    float f[4], vf[4];
+    Elt<T>::unpack(x, f);
+    Elt<VT>::unpack(v, vf);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) vf[i] = __fmul_rn(vf[i], alpha);
+    Pack4<T> tmp;
+    Elt<T>::rd4(vf, tmp);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) f[i] = __fadd_rn(f[i], vf[i]);
+    Elt<T>::rd4(f, x);
+}
+
+// Register-resident implementation: MAXJ = groups of 4 elements per lane; requires H % 128 == 0
+// (every lane owns the same number of groups, so all predicates are warp-uniform) and
+// H <= 128 * MAXJ.  Grid-stride over row vectors, one warp per vector.
 template <typename T, typename VT, int MAXJ, int VARIANT, bool IEEE, bool TAIL, int MINB>
 __global__ void __launch_bounds__(128, MINB) k2_regs_kernel(const K2Params p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *w_s = reinterpret_cast<T *>(smem_raw);
     T *wpost_s = w_s + p.H;  // TAIL only
     const int H = p.H;
-    {
-        // cooperative 8-byte copies of the weight(s) into shared memory
-        const int n4 = H >> 2;
-        for (int g = threadIdx.x; g < n4; g += blockDim.x) {
-            st4<T>(w_s + 4 * g, ld4_ro<T>(static_cast<const T *>(p.w) + 4 * g));
-            if (TAIL) st4<T>(wpost_s + 4 * g, ld4_ro<T>(static_cast<const T *>(p.w_post) + 4 * g));
-        }
+    const int G = H >> 2;
+    const int nj = G >> 5;  // groups per lane (uniform)
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
+        cp_async_group<sizeof(Pack4<T>)>(w_s + 4 * g, static_cast<const T *>(p.w) + 4 * g);
+        if (TAIL) cp_async_group<sizeof(Pack4<T>)>(wpost_s + 4 * g, static_cast<const T *>(p.w_post) + 4 * g);
     }
-    __syncthreads();
 
     const int lane = threadIdx.x & 31;
     const int warps_per_cta = blockDim.x >> 5;
-    const int G = H >> 2;
+    const int stride = gridDim.x * warps_per_cta;
     T *hbase = static_cast<T *>(p.h);
     T *ybase = static_cast<T *>(p.y);
+    const T *src = TAIL ? static_cast<const T *>(p.mlp) : hbase;
 
-    for (int vec = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); vec < p.nvec; vec += gridDim.x * warps_per_cta) {
+    int vec = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
+    Pack4<T> x[MAXJ];
+    // The first row's loads are in flight while the weights land in shared memory.
+    if (vec < p.nvec) {
+#pragma unroll
+        for (int j = 0; j < MAXJ; ++j)
+            if (j < nj) x[j] = ld4<T>(src + (size_t)vec * H + 4 * (lane + 32 * j));
+    }
+    cp_async_wait_all();
+    __syncthreads();
+
+    while (vec < p.nvec) {
         const int row = vec / p.T;
         const int pos = vec - row * p.T;
+        // three independent metadata loads (no dependent chain)
         const int vi = p.row_vec ? __ldg(p.row_vec + row) : -1;
-        const bool steer = vi >= 0 && (p.steer_all || (pos + p.pos0 >= __ldg(p.row_t0 + row)));
-        const float alpha = steer ? __ldg(p.row_alpha + row) : 0.0f;
+        const int t0 = (p.row_vec && !p.steer_all) ? __ldg(p.row_t0 + row) : 0;
+        const float alpha = p.row_vec ? __ldg(p.row_alpha + row) : 0.0f;
+        const bool steer = vi >= 0 && (p.steer_all || (pos + p.pos0 >= t0));
         T *hp = hbase + (size_t)vec * H;
 
-        Pack4<T> x[MAXJ];
-        if (!TAIL) {
-#pragma unroll
-            for (int j = 0; j < MAXJ; ++j) {
-                const int g = lane + 32 * j;
-                if (g < G) x[j] = ld4<T>(hp + 4 * g);
-            }
-        } else {
-            // Gemma-2 block tail: h = rd(residual + gemma_norm(mlp_out; w_post))
-            const T *mp = static_cast<const T *>(p.mlp) + (size_t)vec * H;
-#pragma unroll
-            for (int j = 0; j < MAXJ; ++j) {
-                const int g = lane + 32 * j;
-                if (g < G) x[j] = ld4_ro<T>(mp + 4 * g);
-            }
+        if (TAIL) {
+            // Gemma-2 block tail: h = rd(residual + gemma_norm(mlp_out; w_post)); x holds mlp_out.
             float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-            for (int j = 0; j < MAXJ; ++j) {
-                const int g = lane + 32 * j;
-                if (g < G) {
-                    float f[4];
-                    Elt<T>::unpack(x[j], f);
-                    a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
-                    a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
-                    a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
-                    a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
-                }
-            }
+            for (int j = 0; j < MAXJ; ++j)
+                if (j < nj) sumsq4<T>(x[j], a0, a1, a2, a3);
             const float rm = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
 #pragma unroll
             for (int j = 0; j < MAXJ; ++j) {
-                const int g = lane + 32 * j;
-                if (g < G) {
-                    float f[4], wf[4], rf[4];
-                    Elt<T>::unpack(x[j], f);
-                    Elt<T>::unpack(ld4<T>(wpost_s + 4 * g), wf);
+                if (j < nj) {
+                    const int g = lane + 32 * j;
+                    Pack4<T> n;
+                    norm4<T, IA_NORM_GEMMA>(x[j], rm, ld4<T>(wpost_s + 4 * g), n);
+                    float f[4], rf[4];
+                    Elt<T>::unpack(n, f);
                     Elt<T>::unpack(ld4<T>(hp + 4 * g), rf);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        f[i] = Elt<T>::rd(__fadd_rn(rf[i], norm_out<T, IA_NORM_GEMMA>(f[i], rm, wf[i])));
-                    Elt<T>::pack_exact(f, x[j]);
+                    for (int i = 0; i < 4; ++i) f[i] = __fadd_rn(rf[i], f[i]);
+                    Elt<T>::rd4(f, x[j]);
                 }
             }
         }
 
         if (steer) {
+            // The h' stores may alias the table as far as the compiler knows, so it will not hoist
+            // table loads above them: batch VB loads explicitly to keep VB of them in flight.
             const VT *vp = static_cast<const VT *>(p.vtable) + (size_t)vi * H;
+            constexpr int VB = sizeof(VT) == 4 ? 4 : 8;  // 16 registers of table data in flight per lane
 #pragma unroll
-            for (int j = 0; j < MAXJ; ++j) {
-                const int g = lane + 32 * j;
-                if (g < G) {
-                    float f[4], vf[4];
-                    Elt<T>::unpack(x[j], f);
-                    Elt<VT>::unpack(ld4_ro<VT>(vp + 4 * g), vf);
+            for (int j0 = 0; j0 < MAXJ; j0 += VB) {
+                Pack4<VT> vv[VB];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        f[i] = Elt<T>::rd(__fadd_rn(f[i], Elt<T>::rd(__fmul_rn(vf[i], alpha))));
-                    Elt<T>::pack_exact(f, x[j]);
-                    st4<T>(hp + 4 * g, x[j]);
+                for (int jj = 0; jj < VB; ++jj)
+                    if (j0 + jj < MAXJ && j0 + jj < nj) vv[jj] = ld4_ro<VT>(vp + 4 * (lane + 32 * (j0 + jj)));
+#pragma unroll
+                for (int jj = 0; jj < VB; ++jj) {
+                    if (j0 + jj < MAXJ && j0 + jj < nj) {
+                        inject4<T, VT>(x[j0 + jj], vv[jj], alpha);
+                        st4<T>(hp + 4 * (lane + 32 * (j0 + jj)), x[j0 + jj]);
+                    }
                 }
             }
         } else if (TAIL) {
 #pragma unroll
-            for (int j = 0; j < MAXJ; ++j) {
-                const int g = lane + 32 * j;
-                if (g < G) st4<T>(hp + 4 * g, x[j]);
-            }
+            for (int j = 0; j < MAXJ; ++j)
+                if (j < nj) st4<T>(hp + 4 * (lane + 32 * j), x[j]);
         }
 
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-        for (int j = 0; j < MAXJ; ++j) {
-            const int g = lane + 32 * j;
-            if (g < G) {
-                float f[4];
-                Elt<T>::unpack(x[j], f);
-                a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
-                a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
-                a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
-                a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
-            }
-        }
+        for (int j = 0; j < MAXJ; ++j)
+            if (j < nj) sumsq4<T>(x[j], a0, a1, a2, a3);
         const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
 
         T *yp = ybase + (size_t)vec * H;
 #pragma unroll
         for (int j = 0; j < MAXJ; ++j) {
-            const int g = lane + 32 * j;
-            if (g < G) {
-                float f[4], wf[4];
-                Elt<T>::unpack(x[j], f);
-                Elt<T>::unpack(ld4<T>(w_s + 4 * g), wf);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) f[i] = norm_out<T, VARIANT>(f[i], r, wf[i]);
+            if (j < nj) {
+                const int g = lane + 32 * j;
                 Pack4<T> out;
-                Elt<T>::pack_exact(f, out);
+                norm4<T, VARIANT>(x[j], r, ld4<T>(w_s + 4 * g), out);
                 st4<T>(yp + 4 * g, out);
             }
+        }
+
+        vec += stride;
+        if (vec < p.nvec) {
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j)
+                if (j < nj) x[j] = ld4<T>(src + (size_t)vec * H + 4 * (lane + 32 * j));
         }
     }
 }
@@ -203,40 +243,26 @@ __global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
         const int row = vec / p.T;
         const int pos = vec - row * p.T;
         const int vi = p.row_vec ? __ldg(p.row_vec + row) : -1;
-        const bool steer = vi >= 0 && (p.steer_all || (pos + p.pos0 >= __ldg(p.row_t0 + row)));
-        const float alpha = steer ? __ldg(p.row_alpha + row) : 0.0f;
+        const int t0 = (p.row_vec && !p.steer_all) ? __ldg(p.row_t0 + row) : 0;
+        const float alpha = p.row_vec ? __ldg(p.row_alpha + row) : 0.0f;
+        const bool steer = vi >= 0 && (p.steer_all || (pos + p.pos0 >= t0));
         T *hp = hbase + (size_t)vec * H;
         const VT *vp = static_cast<const VT *>(p.vtable) + (size_t)(steer ? vi : 0) * H;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         for (int g = lane; g < G; g += 32) {
-            float f[4];
-            Elt<T>::unpack(ld4<T>(hp + 4 * g), f);
+            Pack4<T> x = ld4<T>(hp + 4 * g);
             if (steer) {
-                float vf[4];
-                Elt<VT>::unpack(ld4_ro<VT>(vp + 4 * g), vf);
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    f[i] = Elt<T>::rd(__fadd_rn(f[i], Elt<T>::rd(__fmul_rn(vf[i], alpha))));
-                Pack4<T> o;
-                Elt<T>::pack_exact(f, o);
-                st4<T>(hp + 4 * g, o);
+                inject4<T, VT>(x, ld4_ro<VT>(vp + 4 * g), alpha);
+                st4<T>(hp + 4 * g, x);
             }
-            a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
-            a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
-            a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
-            a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
+            sumsq4<T>(x, a0, a1, a2, a3);
         }
         const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
         T *yp = ybase + (size_t)vec * H;
         for (int g = lane; g < G; g += 32) {
-            float f[4], wf[4];
-            Elt<T>::unpack(ld4<T>(hp + 4 * g), f);  // own earlier store, or untouched input
-            Elt<T>::unpack(ld4_ro<T>(w + 4 * g), wf);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) f[i] = norm_out<T, VARIANT>(f[i], r, wf[i]);
-            Pack4<T> o;
-            Elt<T>::pack_exact(f, o);
-            st4<T>(yp + 4 * g, o);
+            Pack4<T> out;
+            norm4<T, VARIANT>(ld4<T>(hp + 4 * g) /* own earlier store, or untouched input */, r, ld4_ro<T>(w + 4 * g), out);
+            st4<T>(yp + 4 * g, out);
         }
     }
 }
@@ -261,11 +287,14 @@ static int launch_regs(const K2Params &p, cudaStream_t s) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
     }
-    const int warps = 4;
+    // small problems: fewer warps per CTA so that the rows spread over more SMs
+    const int sms = sm_count();
+    int warps = 4;
+    if ((long)p.nvec < 4L * sms) warps = p.nvec >= 2L * sms ? 2 : 1;
     long ctas = ((long)p.nvec + warps - 1) / warps;
-    const long cap = (long)sm_count() * MINB;
+    const long cap = (long)sms * MINB;
     if (ctas > cap) ctas = cap;
-    kern<<<(unsigned)ctas, 128, smem, s>>>(p);
+    kern<<<(unsigned)ctas, 32 * warps, smem, s>>>(p);
     return (int)cudaGetLastError();
 }
 
@@ -273,13 +302,18 @@ template <typename T, typename VT, int VARIANT, bool IEEE, bool TAIL>
 static int dispatch_h(const K2Params &p, cudaStream_t s) {
     const int per_lane = ((p.H >> 2) + 31) / 32;
     constexpr bool wide = sizeof(T) == 4;
-    if (per_lane <= 8) return launch_regs<T, VT, 8, VARIANT, IEEE, TAIL, wide ? 6 : 8>(p, s);
-    if (per_lane <= 16) return launch_regs<T, VT, 16, VARIANT, IEEE, TAIL, wide ? 4 : 6>(p, s);
-    if constexpr (!wide) {
-        if (per_lane <= 28) return launch_regs<T, VT, 28, VARIANT, IEEE, TAIL, 4>(p, s);
-        if (per_lane <= 32) return launch_regs<T, VT, 32, VARIANT, IEEE, TAIL, 4>(p, s);
-        if (per_lane <= 40) return launch_regs<T, VT, 40, VARIANT, IEEE, TAIL, 3>(p, s);
-        if (per_lane <= 64) return launch_regs<T, VT, 64, VARIANT, IEEE, TAIL, 2>(p, s);
+    const bool even = (p.H & 127) == 0;  // the register kernel wants the same group count on every lane
+    if (!even) {
+        if (TAIL) return IA_ERR_SHAPE;
+    } else if (per_lane <= 8) return launch_regs<T, VT, 8, VARIANT, IEEE, TAIL, wide ? 4 : 8>(p, s);
+    else if (per_lane <= 16) return launch_regs<T, VT, 16, VARIANT, IEEE, TAIL, wide ? 3 : 6>(p, s);
+    if constexpr (!wide) if (even) {
+        // one CTA fewer per SM when extra registers are live (fp32 table groups, Gemma-2 tail)
+        constexpr int D = (TAIL || sizeof(VT) == 4) ? 1 : 0;
+        if (per_lane <= 28) return launch_regs<T, VT, 28, VARIANT, IEEE, TAIL, 5 - D>(p, s);
+        if (per_lane <= 32) return launch_regs<T, VT, 32, VARIANT, IEEE, TAIL, 5 - D>(p, s);
+        if (per_lane <= 40) return launch_regs<T, VT, 40, VARIANT, IEEE, TAIL, 4 - D>(p, s);
+        if (per_lane <= 64) return launch_regs<T, VT, 64, VARIANT, IEEE, TAIL, 3 - D>(p, s);
     }
     if (TAIL) return IA_ERR_TOO_LARGE;
     long ctas = ((long)p.nvec + 3) / 4;

@@ -1,0 +1,409 @@
+"""Decode runtime around the two kernels: one process per GPU, static KV cache, one CUDA graph per
+decode step, the steering kernel (K2) sitting where the reference had a forward hook.
+
+What is stock and what is ours (north_star: "model GEMMs left to stock cuBLAS"):
+  * stock: every Hugging Face sub-module of the decoder layer — q/k/v/o/MLP `nn.Linear` (cuBLAS),
+    rotary embedding, SDPA attention, the RMSNorms that are NOT fused — called exactly as
+    `LlamaDecoderLayer.forward` / `Qwen2DecoderLayer.forward` / `Gemma2DecoderLayer.forward` call them,
+    so the numerics outside the hot path are the reference's;
+  * ours: the layer loop (no `model.generate`, no hooks, no per-row Python loops), the KV cache
+    (preallocated, exact-length views, so attention never touches masked tail slots), per-step CUDA
+    graphs, and at layer L the fused injection + next-RMSNorm kernel in place of
+    reference model_utils.py:750-808 + the next layer's `input_layernorm` (or `model.norm`).
+
+The reference drives `model.generate` with a hook (reference model_utils.py:811-847); the forward
+hook fires once for the prompt and once per cached decode step, which is exactly
+the call pattern of `Session.generate` below.
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import kernels
+
+
+@dataclass
+class SteerSpec:
+    """Per-row steering for one batch: row b adds alpha[b] * vtable[row_vec[b]] at layer
+    `layer_idx` from absolute position row_t0[b] on (prompt) and at every generated token.
+    row_vec[b] < 0 marks a control row; row_t0 None steers every position
+    (reference model_utils.py:798-802)."""
+
+    layer_idx: int
+    vtable: torch.Tensor              # [n_vec, H] model dtype or fp32, on the device
+    row_vec: torch.Tensor             # [B] int32
+    row_alpha: torch.Tensor           # [B] float32
+    row_t0: Optional[torch.Tensor]    # [B] int32 absolute (pad-shifted) start, or None
+
+
+class StaticKV:
+    """Preallocated K/V with the `update(k, v, layer_idx)` method HF attention modules call.
+    `pos` is a host integer, so the returned views have exact length — the same shapes a
+    DynamicCache would hand to SDPA — and are static inside a per-step CUDA graph."""
+
+    def __init__(self, n_layers: int, batch: int, n_kv: int, max_len: int, head_dim: int, dtype, device):
+        self.k = [torch.empty(batch, n_kv, max_len, head_dim, dtype=dtype, device=device) for _ in range(n_layers)]
+        self.v = [torch.empty(batch, n_kv, max_len, head_dim, dtype=dtype, device=device) for _ in range(n_layers)]
+        self.pos = 0
+        self.max_len = max_len
+
+    def update(self, key_states, value_states, layer_idx, *args, **kwargs):
+        t = key_states.shape[2]
+        end = self.pos + t
+        if end > self.max_len:
+            raise RuntimeError("StaticKV overflow")
+        self.k[layer_idx][:, :, self.pos:end].copy_(key_states)
+        self.v[layer_idx][:, :, self.pos:end].copy_(value_states)
+        return self.k[layer_idx][:, :, :end], self.v[layer_idx][:, :, :end]
+
+    def bytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in self.k + self.v)
+
+
+class DecoderEngine:
+    """Layer loop over a Hugging Face Llama / Qwen2 / Gemma-2 causal LM."""
+
+    def __init__(self, model, fuse_gemma_tail: bool = True):
+        self.model = model
+        inner = model.model
+        if not hasattr(inner, "layers") and hasattr(inner, "language_model"):
+            inner = inner.language_model  # reference model_utils.py:287-289
+        self.inner = inner
+        self.layers = list(inner.layers)
+        self.n_layers = len(self.layers)
+        cfg = model.config
+        self.cfg = cfg
+        first = self.layers[0]
+        self.is_gemma2 = hasattr(first, "pre_feedforward_layernorm")
+        self.variant = "gemma" if "gemma" in type(model).__name__.lower() else "llama"
+        self.fuse_gemma_tail = fuse_gemma_tail and self.is_gemma2
+        norm0 = first.input_layernorm
+        self.eps = float(getattr(norm0, "variance_epsilon", getattr(norm0, "eps", 1e-6)))
+        p = next(model.parameters())
+        self.device, self.dtype = p.device, p.dtype
+        self.hidden = cfg.hidden_size
+        self.n_kv = cfg.num_key_value_heads
+        self.head_dim = getattr(cfg, "head_dim", None) or cfg.hidden_size // cfg.num_attention_heads
+        self.softcap = getattr(cfg, "final_logit_softcapping", None)
+        self.sliding_window = getattr(cfg, "sliding_window", None) if self.is_gemma2 else None
+        self.counters = {"k2_launches": 0, "k1_launches": 0}
+
+    # -- masks / positions --------------------------------------------------------------------
+    @staticmethod
+    def position_ids(attention_mask: torch.Tensor) -> torch.Tensor:
+        pos = attention_mask.long().cumsum(-1) - 1
+        return pos.masked_fill(attention_mask == 0, 1)
+
+    def _layer_kind(self, i: int) -> str:
+        # transformers Gemma2Model.forward picks the mask by config.layer_types[i]
+        kinds = getattr(self.cfg, "layer_types", None)
+        return kinds[i] if kinds else "full_attention"
+
+    def prefill_masks(self, attention_mask: torch.Tensor) -> Dict[str, Optional[torch.Tensor]]:
+        """4-D boolean masks [B,1,T,T] (True = attend): causal AND key-not-padding, plus the window
+        for Gemma-2 sliding layers.  None when nothing is padded (SDPA then runs is_causal)."""
+        b, t = attention_mask.shape
+        valid = attention_mask.bool()
+        need_window = self.sliding_window is not None and t > self.sliding_window
+        if bool(valid.all()) and not need_window:
+            return {"full_attention": None, "sliding_attention": None}
+        q = torch.arange(t, device=attention_mask.device)
+        causal = q[None, :] <= q[:, None]
+        full = (causal[None, None] & valid[:, None, None, :])
+        out = {"full_attention": None if bool(valid.all()) else full, "sliding_attention": None if bool(valid.all()) else full}
+        if need_window:
+            win = (q[:, None] - q[None, :]) < self.sliding_window
+            out["sliding_attention"] = full & win[None, None]
+        return out
+
+    # -- the layer loop -----------------------------------------------------------------------
+    def run_layers(self, h: torch.Tensor, pos_emb, masks, cache, steer: Optional[SteerSpec] = None,
+                   pos0: int = 0, decode: bool = False, stop_after: Optional[int] = None,
+                   capture: Optional[Sequence[int]] = None):
+        """Runs decoder layers on h [B,T,H].  Returns (final_normed_or_None, captured dict).
+        With `stop_after` the loop ends after that layer and nothing is normed."""
+        captured: Dict[int, torch.Tensor] = {}
+        want = set(capture or ())
+        last = self.n_layers - 1 if stop_after is None else stop_after
+        normed_in = None  # y from K2 = already-normed input of the next layer
+        final = None
+        for i in range(last + 1):
+            layer = self.layers[i]
+            residual = h
+            x = normed_in if normed_in is not None else layer.input_layernorm(h)
+            normed_in = None
+            attn, _ = layer.self_attn(hidden_states=x, position_embeddings=pos_emb,
+                                      attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
+            steer_here = steer is not None and steer.layer_idx == i
+            if self.is_gemma2:
+                h = residual + layer.post_attention_layernorm(attn)
+                residual = h
+                m = layer.mlp(layer.pre_feedforward_layernorm(h))
+                if steer_here and self.fuse_gemma_tail:
+                    nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
+                    y = kernels.gemma2_tail_inject_rmsnorm(
+                        m.contiguous(), residual, layer.post_feedforward_layernorm.weight, nxt.weight, self.eps,
+                        vtable=steer.vtable, row_vec=steer.row_vec, row_alpha=steer.row_alpha,
+                        row_t0=None if decode else steer.row_t0, pos0=pos0,
+                        steer_all=decode or steer.row_t0 is None)
+                    self.counters["k2_launches"] += 1
+                    h = residual  # updated in place by the kernel
+                    if i + 1 < self.n_layers:
+                        normed_in = y
+                    else:
+                        final = y
+                    if i in want:
+                        captured[i] = h
+                    continue
+                h = residual + layer.post_feedforward_layernorm(m)
+            else:
+                h = residual + attn
+                residual = h
+                h = residual + layer.mlp(layer.post_attention_layernorm(h))
+            if steer_here:
+                nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
+                if not h.is_contiguous():
+                    h = h.contiguous()
+                y = kernels.inject_rmsnorm(h, nxt.weight, self.eps, self.variant, vtable=steer.vtable,
+                                           row_vec=steer.row_vec, row_alpha=steer.row_alpha,
+                                           row_t0=None if decode else steer.row_t0, pos0=pos0,
+                                           steer_all=decode or steer.row_t0 is None)
+                self.counters["k2_launches"] += 1
+                if i + 1 < self.n_layers:
+                    normed_in = y
+                else:
+                    final = y
+            if i in want:
+                captured[i] = h
+        if stop_after is None and final is None:
+            final = self.inner.norm(h)
+        return final, captured
+
+    def logits(self, normed_last: torch.Tensor) -> torch.Tensor:
+        """lm_head (+ Gemma-2 final soft-capping) on [B,1,H] -> [B,V]."""
+        lg = self.model.lm_head(normed_last)
+        if self.softcap is not None:
+            lg = torch.tanh(lg / self.softcap) * self.softcap
+        return lg[:, -1, :]
+
+    # -- extraction ---------------------------------------------------------------------------
+    @torch.inference_mode()
+    def capture_layers(self, input_ids: torch.Tensor, attention_mask: torch.Tensor,
+                       layer_indices: Sequence[int]) -> List[torch.Tensor]:
+        """One forward, stopped after the deepest requested layer; returns the residual stream
+        [B,T,H] after each requested layer (reference model_utils.py:312-338 runs the whole model,
+        once per layer)."""
+        layer_indices = [int(i) for i in layer_indices]
+        for i in layer_indices:
+            if not 0 <= i < self.n_layers:
+                raise IndexError(f"layer {i} out of range")
+        ids = input_ids.to(self.device)
+        mask = attention_mask.to(self.device)
+        h = self.inner.embed_tokens(ids)
+        pos = self.position_ids(mask)
+        pos_emb = self.inner.rotary_emb(h, pos)
+        _, got = self.run_layers(h, pos_emb, self.prefill_masks(mask), None, stop_after=max(layer_indices),
+                                 capture=layer_indices)
+        return [got[i] for i in layer_indices]
+
+    @torch.inference_mode()
+    def extract_vectors(self, concept_ids, concept_mask, base_ids, base_mask, layer_indices: Sequence[int],
+                        mode: str = "baseline", normalize: bool = False, token_idx: int = -1, want_f32: bool = True):
+        """K1 over any number of layers: two forwards (concept batch, baseline batch — the
+        reference also runs them separately, vector_utils.py:524-540) and one fused
+        gather + mean-diff + norm launch.  Returns (v_f32, v_rounded, norm) on the device,
+        each [n_layers, n_out, H] / [n_layers, n_out]."""
+        if not self.device.type == "cuda":
+            raise RuntimeError("concept-vector extraction needs the CUDA kernels; there is no CPU path")
+        cl = self.capture_layers(concept_ids, concept_mask, layer_indices)
+        bl = None
+        if mode not in ("no_baseline", "raw"):
+            bl = self.capture_layers(base_ids, base_mask, layer_indices)
+
+        def tok(t_len, n):
+            t = token_idx if token_idx >= 0 else t_len + token_idx  # reference slices the padded tensor
+            return torch.full((n,), t, dtype=torch.int32)
+
+        out = kernels.gather_meandiff(
+            cl, bl, mode, normalize, concept_tok=tok(cl[0].shape[1], cl[0].shape[0]),
+            base_tok=None if bl is None else tok(bl[0].shape[1], bl[0].shape[0]), want_f32=want_f32)
+        self.counters["k1_launches"] += 1
+        return out
+
+    # -- generation ---------------------------------------------------------------------------
+    def session(self, batch: int, prompt_len: int, max_new_tokens: int, padded: bool, n_vec_cap: int = 64,
+                vec_dtype: Optional[torch.dtype] = None, use_graphs: Optional[bool] = None) -> "Session":
+        key = (batch, prompt_len, max_new_tokens, padded, n_vec_cap, vec_dtype)
+        cur = getattr(self, "_session", None)
+        if cur is not None and cur.key == key:
+            return cur
+        self._session = None  # free the old KV cache / graphs before allocating
+        if self.device.type == "cuda":
+            torch.cuda.empty_cache()
+        self._session = Session(self, key, use_graphs)
+        return self._session
+
+
+class Session:
+    """Static buffers + per-step CUDA graphs for one (batch, prompt_len, max_new_tokens) shape."""
+
+    def __init__(self, eng: DecoderEngine, key, use_graphs: Optional[bool]):
+        self.eng, self.key = eng, key
+        b, t, n, padded, n_vec_cap, vec_dtype = key
+        dev = eng.device
+        self.B, self.T, self.N, self.padded = b, t, n, padded
+        self.cache = StaticKV(eng.n_layers, b, eng.n_kv, t + max(n - 1, 0), eng.head_dim, eng.dtype, dev)
+        self.key_valid = torch.ones(b, t + n, dtype=torch.bool, device=dev)
+        self.tok = torch.zeros(b, 1, dtype=torch.long, device=dev)
+        self.posid = torch.zeros(b, 1, dtype=torch.long, device=dev)
+        self.out_ids = torch.zeros(b, n, dtype=torch.long, device=dev)
+        self.logits_buf: Optional[torch.Tensor] = None
+        self.unfinished = torch.ones(b, dtype=torch.bool, device=dev)
+        self.vtable = torch.zeros(n_vec_cap, eng.hidden, dtype=vec_dtype or eng.dtype, device=dev)
+        self.row_vec = torch.full((b,), -1, dtype=torch.int32, device=dev)
+        self.row_alpha = torch.zeros(b, dtype=torch.float32, device=dev)
+        self.row_t0 = torch.zeros(b, dtype=torch.int32, device=dev)
+        self.use_graphs = (dev.type == "cuda") if use_graphs is None else use_graphs
+        self.graphs: Dict[Tuple, List] = {}
+        self.pool = None
+        self.step_logits: List[torch.Tensor] = []
+
+    # one cached decode step: feeds self.tok at cache position T+s-1, leaves next token in self.tok
+    def _step(self, s: int, steer: Optional[SteerSpec], greedy: bool, eos: Optional[int], pad: int):
+        eng = self.eng
+        eng_cache = self.cache
+        eng_cache.pos = self.T + s - 1
+        length = self.T + s
+        h = eng.inner.embed_tokens(self.tok)
+        pos_emb = eng.inner.rotary_emb(h, self.posid)
+        full = self.key_valid[:, None, None, :length] if self.padded else None
+        masks = {"full_attention": full, "sliding_attention": full}
+        if eng.sliding_window is not None and length > eng.sliding_window:
+            k = torch.arange(length, device=h.device)
+            win = (k > length - 1 - eng.sliding_window)[None, None, None, :]
+            masks["sliding_attention"] = win.expand(self.B, 1, 1, length) if full is None else (full & win)
+        final, _ = eng.run_layers(h, pos_emb, masks, eng_cache, steer=steer, pos0=self.T + s - 1, decode=True)
+        lg = eng.logits(final)
+        if self.logits_buf is not None:
+            self.logits_buf.copy_(lg)
+        if greedy:
+            nxt = lg.argmax(dim=-1)
+            self._commit(nxt, s, eos, pad)
+
+    def _commit(self, nxt: torch.Tensor, s: int, eos: Optional[int], pad: int):
+        if eos is not None:
+            nxt = torch.where(self.unfinished, nxt, torch.full_like(nxt, pad))
+            self.unfinished &= nxt != eos
+        self.out_ids[:, s].copy_(nxt)
+        self.tok.copy_(nxt[:, None])
+        self.posid.add_(1)
+
+    def _ensure_graphs(self, gkey, steer, greedy, eos, pad):
+        if gkey in self.graphs:
+            return self.graphs[gkey]
+        # warm-up on a side stream (lazy cuBLAS/SDPA init must not happen under capture)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self._step(1, steer, greedy, eos, pad)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graphs = []
+        for s in range(1, self.N):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, pool=self.pool):
+                self._step(s, steer, greedy, eos, pad)
+            if self.pool is None:
+                self.pool = g.pool()
+            graphs.append(g)
+        self.graphs[gkey] = graphs
+        return graphs
+
+    @torch.inference_mode()
+    def generate(self, input_ids: torch.Tensor, attention_mask: torch.Tensor, steer: Optional[SteerSpec] = None,
+                 temperature: float = 0.0, top_k: Optional[int] = 50, eos_token_id: Optional[int] = None,
+                 pad_token_id: int = 0, generator: Optional[torch.Generator] = None,
+                 keep_logits: bool = False) -> torch.Tensor:
+        """Prefill + N-1 cached decode steps.  Returns new token ids [B, N] (device tensor owned by
+        the session; clone to keep).  With keep_logits, self.step_logits holds [N] x [B,V] float32."""
+        eng = self.eng
+        ids = input_ids.to(eng.device, non_blocking=True)
+        mask = attention_mask.to(eng.device, non_blocking=True)
+        assert ids.shape == (self.B, self.T), (ids.shape, self.B, self.T)
+        greedy = temperature <= 0
+        self.step_logits = []
+        st = None
+        if steer is not None:
+            if steer.vtable.device.type != "cuda":
+                raise RuntimeError("steering needs the CUDA kernels; there is no CPU path")
+            n_vec = steer.vtable.shape[0]
+            self.vtable[:n_vec].copy_(steer.vtable, non_blocking=True)
+            self.row_vec.copy_(steer.row_vec, non_blocking=True)
+            self.row_alpha.copy_(steer.row_alpha, non_blocking=True)
+            if steer.row_t0 is not None:
+                self.row_t0.copy_(steer.row_t0, non_blocking=True)
+            st = SteerSpec(steer.layer_idx, self.vtable, self.row_vec, self.row_alpha,
+                           self.row_t0 if steer.row_t0 is not None else None)
+        self.key_valid[:, : self.T].copy_(mask.bool())
+        self.unfinished.fill_(True)
+
+        # ---- prefill (eager: one pass of large GEMMs) ----
+        self.cache.pos = 0
+        h = eng.inner.embed_tokens(ids)
+        pos = eng.position_ids(mask)
+        pos_emb = eng.inner.rotary_emb(h, pos)
+        final, _ = eng.run_layers(h, pos_emb, eng.prefill_masks(mask), self.cache, steer=st, pos0=0, decode=False)
+        lg = eng.logits(final[:, -1:, :])
+        if keep_logits:
+            self.step_logits.append(lg.float().clone())
+        self.posid.copy_((mask.long().sum(-1, keepdim=True)) - 1)  # position of the last prompt token
+        nxt = lg.argmax(dim=-1) if greedy else self._sample(lg, temperature, top_k, generator)
+        self._commit(nxt, 0, eos_token_id, pad_token_id)  # also advances posid to the new token's position
+
+        # ---- decode ----
+        if self.N > 1:
+            want_buf = keep_logits or not greedy
+            if want_buf and self.logits_buf is None:
+                self.logits_buf = torch.empty(self.B, lg.shape[-1], dtype=lg.dtype, device=eng.device)
+                self.graphs.clear()
+            graphs = None
+            if self.use_graphs:
+                gkey = (None if st is None else (st.layer_idx, st.row_t0 is None), greedy, eos_token_id, pad_token_id,
+                        self.logits_buf is not None)
+                if gkey not in self.graphs:
+                    # capturing runs warm-up steps that scribble on the state: save and restore it
+                    keep = (self.tok.clone(), self.posid.clone(), self.out_ids.clone(), self.unfinished.clone())
+                    graphs = self._ensure_graphs(gkey, st, greedy, eos_token_id, pad_token_id)
+                    for dst, src in zip((self.tok, self.posid, self.out_ids, self.unfinished), keep):
+                        dst.copy_(src)
+                graphs = self.graphs[gkey]
+            for s in range(1, self.N):
+                if graphs is not None:
+                    graphs[s - 1].replay()
+                else:
+                    self._step(s, st, greedy, eos_token_id, pad_token_id)
+                if keep_logits:
+                    self.step_logits.append(self.logits_buf.float().clone())
+                if not greedy:
+                    nxt = self._sample(self.logits_buf, temperature, top_k, generator)
+                    self._commit(nxt, s, eos_token_id, pad_token_id)
+                if eos_token_id is not None and s % 16 == 0 and not bool(self.unfinished.any()):
+                    self.out_ids[:, s + 1:].fill_(pad_token_id)
+                    break
+        return self.out_ids
+
+    @staticmethod
+    def _sample(logits: torch.Tensor, temperature: float, top_k: Optional[int], generator) -> torch.Tensor:
+        """HF `do_sample=True` defaults: temperature, then top-k 50, then multinomial
+        (reference model_utils.py:833-837 passes only temperature)."""
+        lg = logits.float() / temperature
+        if top_k is not None and 0 < top_k < lg.shape[-1]:
+            kth = lg.topk(top_k, dim=-1).values[..., -1:]
+            lg = lg.masked_fill(lg < kth, float("-inf"))
+        probs = torch.softmax(lg, dim=-1)
+        return torch.multinomial(probs, 1, generator=generator).squeeze(-1)

@@ -1,0 +1,82 @@
+"""Trial-grid scheduler: one large steered batch per layer, a different (concept, alpha, t0) per row.
+
+Replaces the reference's nested loops (detect_injected_thoughts.py:1645-1647 layer x strength,
+:1797-1866 injection batches, :1908-1952 control batches, :1973-2042 forced batches), where
+every (layer, strength) pair is a separate sequence of `generate` calls with ONE scalar strength
+per call (reference model_utils.py:692).  Here all strengths, concepts and trials of a layer ride
+in the same batch — control trials too, as rows whose vector index is -1 — and layers are the unit
+that is sharded across GPUs (parallel.py).
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, Iterable, List, Optional, Sequence
+
+import torch
+
+from . import steering_utils as su
+
+
+@dataclass(frozen=True)
+class Trial:
+    concept: str
+    strength: float      # 0.0 for control rows
+    trial: int
+    kind: str            # "injection" | "control" | "forced"
+
+
+def layer_trials(concepts: Sequence[str], strengths: Sequence[float], n_injection: int, n_control: int = 0,
+                 n_forced: int = 0, dedupe_control: bool = True) -> List[Trial]:
+    """Rows of one layer's batch, concept-major like the reference's task lists
+    (detect_injected_thoughts.py:1797-1799).  Control trials depend on neither layer nor strength;
+    the reference regenerates them for every (layer, strength) (:1908 sits inside both loops) —
+    with dedupe_control they appear once per layer batch instead of once per strength."""
+    rows: List[Trial] = []
+    for a in strengths:
+        rows += [Trial(c, float(a), t, "injection") for c in concepts for t in range(1, n_injection + 1)]
+        rows += [Trial(c, float(a), t, "forced") for c in concepts for t in range(1, n_forced + 1)]
+        if not dedupe_control:
+            rows += [Trial(c, 0.0, t, "control") for c in concepts for t in range(1, n_control + 1)]
+    if dedupe_control:
+        rows += [Trial(c, 0.0, t, "control") for c in concepts for t in range(1, n_control + 1)]
+    return rows
+
+
+def chunk(rows: Sequence[Trial], batch_size: int) -> Iterable[Sequence[Trial]]:
+    for i in range(0, len(rows), batch_size):
+        yield rows[i:i + batch_size]
+
+
+def run_layer(model, layer_idx: int, vectors: Dict[str, torch.Tensor], rows: Sequence[Trial], max_new_tokens: int = 100,
+              temperature: float = 1.0, batch_size: int = 256, layer_fraction: Optional[float] = None) -> List[dict]:
+    """Generate every row of one layer and return result dicts in the reference's schema
+    (detect_injected_thoughts.py:1871-1881)."""
+    concepts = list(vectors.keys())
+    cidx = {c: i for i, c in enumerate(concepts)}
+    table = torch.stack([vectors[c].reshape(-1) for c in concepts])
+    results: List[dict] = []
+    prompt_cache: Dict[tuple, tuple] = {}
+    for part in chunk(rows, batch_size):
+        prompts, starts = [], []
+        for r in part:
+            key = (r.trial, r.kind == "forced")
+            if key not in prompt_cache:
+                p = su.format_trial_prompt(model, r.trial, forced=key[1])
+                prompt_cache[key] = (p, su.steering_start_position(model, p, r.trial, missing=0))
+            p, t0 = prompt_cache[key]
+            prompts.append(p)
+            starts.append(t0)
+        ids, mask = model._encode(prompts)
+        row_vec = [cidx[r.concept] if r.kind != "control" else -1 for r in part]
+        alphas = [r.strength for r in part]
+        new_ids = model.steered_generate_ids(ids, mask, layer_idx, table, row_vec, alphas, starts, max_new_tokens,
+                                             temperature)
+        texts = model._decode_rows(new_ids, ids, mask)
+        for r, text in zip(part, texts):
+            results.append({
+                "concept": r.concept, "trial": r.trial, "response": text, "injected": r.kind != "control",
+                "layer": layer_idx, "layer_fraction": layer_fraction, "strength": r.strength,
+                "detected": su.check_concept_mentioned(text, r.concept), "trial_type": r.kind,
+            })
+    return results

@@ -1,0 +1,188 @@
+"""End-to-end parity of the B200 runtime on the GPU.
+
+north_star's bar: concept vectors within 1e-3 relative L2 of the reference; steered next-token
+logits within 2e-2 max-abs of the reference hook path with identical greedy tokens for the first
+32 steps, on synthetic prompts and random-init weights.
+
+Two anchors:
+  (a) the restated reference hook path (oracle/ref_hooks.py: HF `generate` + forward hook, pinned
+      bit-for-bit to the real reference by oracle/make_golden.py) run on the SAME GPU and dtype;
+  (b) the committed outputs of the real reference run on the CPU (tests/golden/e2e_*.npz,
+      config1_*.npz).  fp32 cases must reproduce the reference's greedy ids exactly; bf16 cases
+      differ from a CPU run by GEMM rounding, so there the bound is the 2e-2 logit tolerance on the
+      first step (later steps may legitimately follow a different greedy path).
+"""
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, widen
+from oracle import ref_hooks
+
+pytestmark = pytest.mark.gpu
+
+DT = {"bf16": torch.bfloat16, "f32": torch.float32}
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    return "cuda:0"
+
+
+def _wrapper(arch, dtype, seed, **overrides):
+    from introspective_awareness_b200.model_utils import ModelWrapper
+
+    return ModelWrapper.from_arch(arch, device=_dev(), dtype=dtype, seed=seed, **overrides)
+
+
+def _ours(w, g_ids, g_mask, layer, vec_table, alphas, t0, n_new):
+    ids = torch.from_numpy(g_ids)
+    mask = torch.from_numpy(g_mask)
+    out = w.steered_generate_ids(ids, mask, layer, vec_table, list(range(vec_table.shape[0])), alphas, t0, n_new,
+                                 temperature=0.0, keep_logits=True)
+    return out.cpu().numpy(), torch.stack(w.last_session.step_logits).cpu()
+
+
+@pytest.mark.parametrize("name", ["e2e_qwen2_f32.npz", "e2e_gemma2_f32.npz", "e2e_llama_bf16.npz", "e2e_qwen2_bf16.npz",
+                                  "e2e_gemma2_bf16.npz", "e2e_llama_bf16_lastlayer_a3.npz", "e2e_llama_bf16_h1024.npz",
+                                  "e2e_llama_bf16_allpos.npz"])
+def test_against_real_reference_outputs(name):
+    g = load_golden(name)
+    dtn = str(g["dtype"])
+    overrides = eval(str(g["overrides"]), {"__builtins__": {}})
+    w = _wrapper(str(g["arch"]), DT[dtn], int(g["seed"]), **overrides)
+    layer = int(g["layer_idx"])
+    # extraction through K1 (two forwards + one fused launch), same token ids the reference saw
+    v32, vr, _ = w.engine.extract_vectors(torch.from_numpy(g["concept_ids"]), torch.from_numpy(g["concept_mask"]),
+                                          torch.from_numpy(g["base_ids"]), torch.from_numpy(g["base_mask"]), [layer])
+    want = torch.from_numpy(widen(g["vectors"], dtn))
+    got = vr[0].float().cpu()
+    rel = ((got - want).norm(dim=1) / want.norm(dim=1)).max().item()
+    assert rel <= (1e-3 if dtn == "f32" else 2e-2), rel  # bf16: CPU-vs-GPU GEMM rounding upstream of K1
+    # steering with the REFERENCE's vectors, so this half does not inherit extraction differences
+    table = want.to(DT[dtn])
+    t0 = None if bool(g["steer_all"]) else g["t0"].tolist()
+    n_new = int(g["n_new"])
+    ids, logits = _ours(w, g["input_ids"], g["attention_mask"], layer, table, [float(g["alpha"])] * table.shape[0], t0, n_new)
+    ref_logits = torch.from_numpy(g["logits"])
+    if dtn == "f32":
+        assert (logits - ref_logits).abs().max().item() <= 2e-3
+        assert np.array_equal(ids, g["new_ids"])
+    else:
+        assert (logits[0] - ref_logits[0]).abs().max().item() <= 2e-2
+        same = (ids == g["new_ids"]).all(axis=1)
+        # rows that followed the same greedy path must agree on every step's logits
+        for r in np.nonzero(same)[0]:
+            assert (logits[:, r] - ref_logits[:, r]).abs().max().item() <= 4e-2
+
+
+def test_config1_qwen05b_fp32_matches_real_reference():
+    """BASELINE.json configs[0]: what the reference produced on the CPU, reproduced on the B200."""
+    g = load_golden("config1_qwen05b_f32.npz")
+    w = _wrapper("qwen2.5-0.5b", torch.float32, int(g["seed"]))
+    layer = int(g["layer_idx"])
+    assert layer == 16
+    _, vr, _ = w.engine.extract_vectors(torch.from_numpy(g["concept_ids"]), torch.from_numpy(g["concept_mask"]),
+                                        torch.from_numpy(g["base_ids"]), torch.from_numpy(g["base_mask"]), [layer])
+    want = torch.from_numpy(g["vectors"])
+    rel = ((vr[0].float().cpu() - want).norm(dim=1) / want.norm(dim=1)).max().item()
+    assert rel <= 1e-3, rel
+    ids, logits = _ours(w, g["input_ids"], g["attention_mask"], layer, vr[0], [float(g["alpha"])] * 4, g["t0"].tolist(), 32)
+    assert np.array_equal(ids, g["new_ids"])
+    top_idx = torch.from_numpy(g["top_indices"]).long()
+    got_top = torch.gather(logits, 2, top_idx)
+    assert (got_top - torch.from_numpy(g["top_values"])).abs().max().item() <= 2e-3
+
+
+def _hook_path_vs_ours(arch, layer, rows, t_max, t_min, n_new, alphas, seed, n_concepts=50, **overrides):
+    from introspective_awareness_b200.synthetic import synthetic_prompt_ids
+
+    w = _wrapper(arch, torch.bfloat16, seed, **overrides)
+    V = w.model.config.vocab_size
+    ids, mask, lens = synthetic_prompt_ids(rows, t_max, t_min, V, seed=1)
+    gen = torch.Generator().manual_seed(5)
+    table = (torch.randn(n_concepts, w.engine.hidden, generator=gen) * 0.5).to(torch.bfloat16)
+    t0 = (lens - min(28, t_min - 1)).tolist()
+    row_vec = [i % n_concepts for i in range(rows)]
+    row_alpha = [alphas[(i // n_concepts) % len(alphas)] for i in range(rows)]
+    ours = w.steered_generate_ids(ids, mask, layer, table, row_vec, row_alpha, t0, n_new, temperature=0.0, keep_logits=True)
+    ours = ours.cpu()
+    our_logits = torch.stack(w.last_session.step_logits).cpu()
+    # reference hook path: one call per distinct alpha with the SAME batch
+    ref_ids = torch.zeros_like(ours)
+    ref_logits = torch.zeros_like(our_logits)
+    for a in sorted(set(row_alpha)):
+        out = ref_hooks.steered_generate(w.model, ids, mask, layer, [table[j] for j in row_vec], a, t0, n_new,
+                                         want_logits=True)
+        sel = torch.tensor([x == a for x in row_alpha])
+        ref_ids[sel] = out["new_ids"][sel]
+        ref_logits[:, sel] = out["logits"][:, sel]
+    return ours, our_logits, ref_ids, ref_logits
+
+
+@pytest.mark.parametrize("arch,layer", [("tiny-llama", 1), ("tiny-qwen2", 2), ("tiny-gemma2", 1), ("tiny-llama", 3)])
+def test_same_device_hook_path_tiny(arch, layer):
+    ours, ol, ref, rl = _hook_path_vs_ours(arch, layer, rows=24, t_max=40, t_min=30, n_new=32, alphas=[1.0, 3.0, 8.0],
+                                           seed=11, n_concepts=8)
+    assert (ol - rl).abs().max().item() <= 2e-2
+    assert torch.equal(ours, ref)
+
+
+def test_same_device_hook_path_llama_8b_dims():
+    """Real Llama-3.1-8B hidden size / heads / vocabulary (4 layers), BASELINE configs[1] row count:
+    200 rows = 50 concepts x 4 strengths in ONE batch vs four reference calls."""
+    ours, ol, ref, rl = _hook_path_vs_ours("llama-8b-4layer", 2, rows=200, t_max=128, t_min=112, n_new=32,
+                                           alphas=[1.0, 2.0, 4.0, 8.0], seed=3)
+    diff = (ol - rl).abs().max().item()
+    same_rows = (ours == ref).all(dim=1).float().mean().item()
+    print(f"max |logit diff| = {diff:.4g}; rows with identical 32-token greedy paths: {same_rows:.3f}")
+    assert diff <= 2e-2
+    assert torch.equal(ours, ref)
+
+
+def test_string_api_matches_hook_path_text():
+    """The reference-facing string surface: same text as the hook path produces (with its A3
+    slicing reproduced via compat_slice)."""
+    from introspective_awareness_b200 import steering_utils as su
+    from introspective_awareness_b200 import vector_utils as vu
+
+    w = _wrapper("tiny-llama", torch.bfloat16, 7)
+    concepts = ["Dust", "Trees", "Oceans"]
+    vecs = vu.extract_concept_vectors_batch(w, concepts, vu.get_baseline_words(10), layer_idx=1)
+    assert all(v.device.type == "cpu" and v.dtype == torch.bfloat16 for v in vecs.values())
+    built = [su.build_trial(w, n) for n in (1, 2, 13)]
+    prompts, t0 = [p for p, _ in built], [t for _, t in built]
+    w.compat_slice = True
+    texts = w.generate_batch_with_multi_steering(prompts, 1, [vecs[c] for c in concepts], strength=4.0,
+                                                 max_new_tokens=12, temperature=0.0, steering_start_positions=t0)
+    enc = w.tokenizer(prompts, return_tensors="pt", padding=True, truncation=True)
+    ref = ref_hooks.steered_generate(w.model, enc["input_ids"], enc["attention_mask"], 1, [vecs[c] for c in concepts],
+                                     4.0, t0, 12)
+    lens = enc["attention_mask"].sum(1).tolist()
+    full = torch.cat([enc["input_ids"], ref["new_ids"]], dim=1)
+    want = [w.tokenizer.decode(full[i, lens[i]:], skip_special_tokens=True).strip() for i in range(3)]
+    assert texts == want
+    # single-prompt surface = batch of one with the same semantics
+    one = w.generate_with_steering(prompts[0], 1, vecs["Dust"], strength=4.0, max_new_tokens=12, temperature=0.0,
+                                   steering_start_pos=t0[0])
+    w.compat_slice = False
+    assert one == w.tokenizer.decode(ref_hooks.steered_generate(
+        w.model, enc["input_ids"][:1, enc["input_ids"].shape[1] - lens[0]:], enc["attention_mask"][:1, enc["input_ids"].shape[1] - lens[0]:],
+        1, [vecs["Dust"]], 4.0, [t0[0]], 12)["new_ids"][0], skip_special_tokens=True).strip()
+    # same-vector batch entry point works (the reference's raises UnboundLocalError)
+    outs = w.generate_batch_with_steering(prompts, 1, vecs["Dust"], strength=2.0, max_new_tokens=4, temperature=0.0,
+                                          steering_start_pos=t0[0])
+    assert len(outs) == 3
+    # sampling path runs and is reproducible under a seeded generator
+    ids, mask = w._encode(prompts)
+    g1 = torch.Generator(device="cuda").manual_seed(3)
+    a = w.steered_generate_ids(ids, mask, 1, torch.stack([vecs[c] for c in concepts]), [0, 1, 2], [4.0] * 3, t0, 8,
+                               temperature=1.0, generator=g1).clone()
+    g2 = torch.Generator(device="cuda").manual_seed(3)
+    b = w.steered_generate_ids(ids, mask, 1, torch.stack([vecs[c] for c in concepts]), [0, 1, 2], [4.0] * 3, t0, 8,
+                               temperature=1.0, generator=g2).clone()
+    assert torch.equal(a, b)

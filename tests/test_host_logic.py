@@ -1,0 +1,175 @@
+"""CPU tests of the host-side mirror of the reference interface: prompt building, t0, grid
+scheduling, the unsteered runtime path (pure torch, no kernels) and the refusal of the steered /
+extraction paths to run without CUDA."""
+
+import inspect
+
+import pytest
+import torch
+
+from introspective_awareness_b200 import grid, model_utils, steering_utils as su, vector_utils as vu
+from introspective_awareness_b200.model_utils import ModelWrapper, get_layer_at_fraction
+from introspective_awareness_b200.stub_tokenizer import StubTokenizer
+
+
+@pytest.fixture(scope="module")
+def wrapper():
+    return ModelWrapper.from_arch("tiny-llama", device="cpu", dtype=torch.float32, seed=3)
+
+
+def test_reference_call_surface_is_present():
+    """Names, positional order and defaults the reference driver relies on."""
+    def params(fn):
+        return [(p.name, p.default) for p in inspect.signature(fn).parameters.values()]
+
+    assert params(vu.extract_concept_vectors_batch) == [
+        ("model", inspect._empty), ("concept_words", inspect._empty), ("baseline_words", inspect._empty),
+        ("layer_idx", inspect._empty), ("extraction_method", "baseline"), ("template", "Tell me about {word}"),
+        ("token_idx", -1), ("normalize", False)]
+    assert params(vu.extract_concept_vector)[-2:] == [("token_idx", -1), ("normalize", False)]
+    assert params(vu.extract_concept_vector_simple)[3:5] == [("control_prompt", "The"), ("template", "{word}")]
+    assert params(ModelWrapper.generate_batch_with_multi_steering)[1:] == [
+        ("prompts", inspect._empty), ("layer_idx", inspect._empty), ("steering_vectors", inspect._empty),
+        ("strength", 1.0), ("max_new_tokens", 512), ("temperature", 0.0), ("steering_start_positions", None),
+        ("debug", False), ("generation_kwargs", inspect._empty)]
+    assert params(ModelWrapper.generate_with_steering)[4:8] == [
+        ("strength", 1.0), ("max_new_tokens", 512), ("temperature", 0.0), ("steering_start_pos", None)]
+    assert params(ModelWrapper.extract_activations)[1:] == [("prompts", inspect._empty), ("layer_idx", inspect._empty),
+                                                            ("token_idx", -1)]
+    assert params(su.run_steered_introspection_test)[4:] == [
+        ("strength", 8.0), ("trial_number", 1), ("max_new_tokens", 100), ("temperature", 1.0), ("is_first_trial", False)]
+    for name in ("run_steered_introspection_test", "run_unsteered_introspection_test",
+                 "run_steered_introspection_test_batch", "run_unsteered_introspection_test_batch",
+                 "run_forced_noticing_test", "run_forced_noticing_test_batch", "calculate_detection_accuracy",
+                 "check_concept_mentioned", "IntrospectionPrompt", "create_introspection_test_prompt"):
+        assert hasattr(su, name), name  # everything detect_injected_thoughts.py:44-49 imports
+    for name in ("create_concept_prompts", "create_contrastive_pair", "cosine_similarity", "save_concept_vector",
+                 "load_concept_vector", "DEFAULT_BASELINE_WORDS", "CONCEPT_PAIRS", "get_baseline_words",
+                 "get_concept_pair", "analyze_vector_underspecification", "extract_concept_vector_with_baseline",
+                 "extract_concept_vector_no_baseline"):
+        assert hasattr(vu, name), name
+
+
+def test_word_lists():
+    words = vu.get_baseline_words()
+    assert len(words) == 100 and words[0] == "Desks" and words[-1] == "Enigmas"
+    assert words.count("Butterflies") == 2  # reference vector_utils.py:398 and :402
+    assert vu.get_baseline_words(10) == words[:10]
+    with pytest.raises(ValueError, match="Unknown concept pair"):
+        vu.get_concept_pair("nope")
+    assert vu.create_concept_prompts("Dust", ["Sand"]) == (["Tell me about Dust"], ["Tell me about Sand"])
+
+
+def test_stub_tokenizer_prefix_property_and_left_padding():
+    tok = StubTokenizer(vocab_size=512)
+    text = "alpha beta\n\nUser: Trial 3: Do you detect?\n\nAssistant:"
+    cut = text.find("Trial 3")
+    full = tok(text, return_tensors="pt")["input_ids"][0].tolist()
+    pre = tok(text[:cut], return_tensors="pt")["input_ids"][0].tolist()
+    assert full[: len(pre)] == pre
+    enc = tok(["a b c", "a"], return_tensors="pt", padding=True, truncation=True)
+    assert enc["attention_mask"].tolist() == [[1, 1, 1], [0, 0, 1]]
+    assert enc["input_ids"][1, :2].tolist() == [0, 0]
+    assert not hasattr(tok, "apply_chat_template") and hasattr(StubTokenizer(chat_template=True), "apply_chat_template")
+
+
+def test_trial_prompt_and_t0(wrapper):
+    prompt, t0 = su.build_trial(wrapper, 7)
+    # plain-text fallback layout of reference steering_utils.py:263-268
+    assert prompt.startswith("I am an interpretability researcher") and prompt.endswith("\n\nAssistant:")
+    assert "Assistant: Ok.\n\nUser: Trial 7: Do you detect an injected thought?" in prompt
+    ids = wrapper.tokenizer(prompt, return_tensors="pt")["input_ids"][0]
+    before = wrapper.tokenizer(prompt[: prompt.find("Trial 7")], return_tensors="pt")["input_ids"][0]
+    assert t0 == len(before) - 1 and 0 < t0 < len(ids)
+    forced, _ = su.build_trial(wrapper, 2, forced=True)
+    assert "Please complete this sentence" in forced and "identify what I inject" in forced
+    assert su.steering_start_position(wrapper, "no marker here", 1) is None
+    assert su.steering_start_position(wrapper, "no marker here", 1, missing=0) == 0
+    chat = ModelWrapper("x", device="cpu", dtype=torch.float32, model=wrapper.model,
+                        tokenizer=StubTokenizer(vocab_size=512, chat_template=True))
+    p2, t2 = su.build_trial(chat, 1)
+    assert "<|user|>" in p2 and p2.endswith("<|assistant|>\n\n") and t2 is not None
+
+
+def test_scoring_helpers():
+    assert su.check_concept_mentioned("I notice dust everywhere", "Dust")
+    assert su.check_concept_mentioned("many trees", "Tree") and su.check_concept_mentioned("a tree", "Trees")
+    assert su.check_concept_mentioned("boxes!", "box") and not su.check_concept_mentioned("industry", "dust")
+    assert su.extract_yes_no_answer("Yes, I do.") is True and su.extract_yes_no_answer("No. Nothing") is False
+    assert su.extract_yes_no_answer("maybe") is None
+    res = [{"injected": True, "detected": True}, {"injected": False, "detected": True},
+           {"injected": True, "detected": None, "response": ""}]
+    assert su.calculate_detection_accuracy(res) == 0.5
+    assert su.calculate_false_positive_rate([{"injected": False, "response": "yes."}, {"injected": False, "response": "no."}]) == 0.5
+
+
+def test_layer_fraction_and_registry(wrapper):
+    assert wrapper.n_layers == 4
+    assert [get_layer_at_fraction(wrapper, f) for f in (0.0, 0.4, 0.7, 0.99, 1.0, 2.0)] == [0, 1, 2, 3, 3, 3]
+    assert wrapper.get_layer_module(2) is wrapper.model.model.layers[2]
+    assert model_utils.MODEL_NAME_MAP["llama_8b"] == "meta-llama/Llama-3.1-8B-Instruct"
+
+
+def test_unsteered_generation_matches_hf_generate(wrapper):
+    """The runtime's own layer loop + static cache against stock `model.generate` (control trials,
+    reference model_utils.py:508-560); padded batch, greedy."""
+    prompts = ["one two three four five six", "seven eight", "nine ten eleven twelve"]
+    enc = wrapper.tokenizer(prompts, return_tensors="pt", padding=True, truncation=True)
+    with torch.no_grad():
+        ref = wrapper.model.generate(**enc, max_new_tokens=9, do_sample=False, pad_token_id=0)
+    texts = wrapper.generate_batch(prompts, max_new_tokens=9, temperature=0.0)
+    width = enc["input_ids"].shape[1]
+    want = [wrapper.tokenizer.decode(ref[i, width:], skip_special_tokens=True).strip() for i in range(3)]
+    assert texts == want
+    # reference string slicing: starts pad_i prompt tokens early
+    wrapper.compat_slice = True
+    try:
+        compat = wrapper.generate_batch(prompts, max_new_tokens=9, temperature=0.0)
+    finally:
+        wrapper.compat_slice = False
+    lens = enc["attention_mask"].sum(1).tolist()
+    assert compat == [wrapper.tokenizer.decode(ref[i, lens[i]:], skip_special_tokens=True).strip() for i in range(3)]
+    assert wrapper.generate(prompts[0], max_new_tokens=4) == wrapper.tokenizer.decode(
+        wrapper.model.generate(**wrapper.tokenizer(prompts[0], return_tensors="pt"), max_new_tokens=4, do_sample=False,
+                               pad_token_id=0)[0, 6:], skip_special_tokens=True)
+
+
+def test_eos_stops_rows_like_hf(wrapper):
+    enc = wrapper.tokenizer(["a b c d", "e f"], return_tensors="pt", padding=True, truncation=True)
+    with torch.no_grad():
+        free = wrapper.model.generate(**enc, max_new_tokens=6, do_sample=False, pad_token_id=0)
+    eos = int(free[0, enc["input_ids"].shape[1] + 2])  # make the 3rd new token of row 0 the EOS
+    wrapper.model.generation_config.eos_token_id = eos
+    try:
+        with torch.no_grad():
+            ref = wrapper.model.generate(**enc, max_new_tokens=6, do_sample=False, pad_token_id=0)
+        got = wrapper.steered_generate_ids(enc["input_ids"], enc["attention_mask"], None, None, None, None, None, 6)
+    finally:
+        wrapper.model.generation_config.eos_token_id = None
+    new = ref[:, enc["input_ids"].shape[1]:]
+    assert torch.equal(got[:, : new.shape[1]].cpu(), new)
+    assert (got[:, new.shape[1]:] == 0).all()
+
+
+def test_hot_path_has_no_cpu_fallback(wrapper):
+    v = torch.zeros(wrapper.engine.hidden)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        wrapper.generate_with_steering("a b c", 1, v, strength=2.0, max_new_tokens=2)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        vu.extract_concept_vectors_batch(wrapper, ["Dust"], ["Sand", "Clay"], layer_idx=1)
+    with pytest.raises(ValueError, match="Unknown extraction method"):
+        vu.extract_concept_vectors_batch(wrapper, ["Dust"], ["Sand"], layer_idx=1, extraction_method="bogus")
+    with pytest.raises(AssertionError, match="one steering vector per prompt"):
+        wrapper.generate_batch_with_multi_steering(["a", "b"], 1, [v])
+
+
+def test_grid_rows_and_dedupe():
+    concepts = [f"c{i}" for i in range(50)]
+    rows = grid.layer_trials(concepts, [1, 2, 4, 8], n_injection=1)
+    assert len(rows) == 200 and {r.strength for r in rows} == {1.0, 2.0, 4.0, 8.0}  # BASELINE configs[1]
+    full = grid.layer_trials(concepts, [1, 2, 4, 8], n_injection=15, n_control=15, n_forced=15, dedupe_control=False)
+    assert len(full) == 4 * 50 * 45  # the reference's per-layer work (detect_injected_thoughts.py:1792-1799)
+    dedup = grid.layer_trials(concepts, [1, 2, 4, 8], n_injection=15, n_control=15, n_forced=15)
+    assert len(dedup) == 4 * 50 * 30 + 50 * 15
+    assert [len(c) for c in grid.chunk(rows, 64)] == [64, 64, 64, 8]
+    assert rows[0] == grid.Trial("c0", 1.0, 1, "injection")

@@ -16,7 +16,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-from introspective_awareness_b200 import kernels  # noqa: E402
+from introspective_awareness_b200 import _lib, kernels  # noqa: E402
 
 PEAK_FALLBACK = 6650.0
 
@@ -60,9 +60,15 @@ def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16):
     t0 = torch.zeros(rows, device=dev, dtype=torch.int32)
     e = h.element_size()
 
-    def fn():
-        kernels.inject_rmsnorm(h, w, 1e-5, variant, vtable=vt, row_vec=row_vec, row_alpha=alpha, row_t0=t0,
-                               steer_all=True, out=y, impl=impl)
+    lib = _lib.load()
+    flags = _lib.IA_STEER_ALL | (_lib.IA_IMPL_TMA if impl == "tma" else 0)
+    args = (h.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(), t0.data_ptr(),
+            w.data_ptr(), 1e-5, rows, T, H, 0, kernels._dt(h), kernels._dt(vt), kernels.VARIANTS[variant], flags,
+            torch.cuda.current_stream().cuda_stream)
+
+    def fn():  # the raw C-ABI call: no per-call Python tensor work inside the timed region
+        rc = lib.ia_inject_rmsnorm(*args)
+        assert rc == 0, rc
 
     ms = time_launch(fn, reps, flush)
     algo = rows * T * H * e * 4 + H * e
@@ -78,9 +84,17 @@ def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16):
     bl = [torch.randn(Nb, T, H, device=dev, generator=g).to(dtype) for _ in range(n_layers)]
     e = cl[0].element_size()
     ws = torch.empty(kernels.workspace_bytes(n_layers, C, Nb, H) + 256, dtype=torch.uint8, device=dev)
+    cptr, bptr = kernels._ptr_table(cl, "c"), kernels._ptr_table(bl, "b")
+    out_r = torch.empty(n_layers, C, H, dtype=dtype, device=dev)
+    out_n = torch.empty(n_layers, C, dtype=torch.float32, device=dev)
+    lib = _lib.load()
+    args = (cptr.data_ptr(), T, 0, 0, C, bptr.data_ptr(), T, 0, 0, Nb, n_layers, H, _lib.IA_MODE_BASELINE, 0, 0,
+            out_r.data_ptr(), out_n.data_ptr(), ws.data_ptr(), ws.numel(), kernels._dt(cl[0]),
+            torch.cuda.current_stream().cuda_stream)
 
     def fn():
-        kernels.gather_meandiff(cl, bl, "baseline", False, want_f32=False, workspace=ws)
+        rc = lib.ia_gather_meandiff(*args)
+        assert rc == 0, rc
 
     ms = time_launch(fn, reps, flush)
     algo = n_layers * ((C + Nb) * H * e + C * H * e)
@@ -102,9 +116,12 @@ def main():
         for rows in rows_ladder:
             if rows * H * 2 * 2 > 40e9:
                 continue
-            r = bench_k2(rows, 1, H, "gemma" if H == 3584 else "llama", args.impl, args.reps, flush)
-            r.update(frac=r["gbs"] / peak, peak=peak, peak_src=src)
-            print(json.dumps(r), flush=True)
+            for cache, fl in (("cold", flush), ("hot", None)):
+                if cache == "hot" and rows * H * 2 * 3 > 100e6:
+                    continue  # larger than L2 anyway
+                r = bench_k2(rows, 1, H, "gemma" if H == 3584 else "llama", args.impl, args.reps, fl)
+                r.update(cache=cache, frac=r["gbs"] / peak, peak=peak, peak_src=src)
+                print(json.dumps(r), flush=True)
     for (L, C, Nb) in ([(32, 50, 100)] if args.quick else [(1, 50, 100), (32, 50, 100), (1, 50, 16334), (1, 50, 262094)]):
         r = bench_k1(L, C, Nb, 4096, args.reps, flush)
         r.update(frac=r["gbs"] / peak, peak=peak, peak_src=src)
