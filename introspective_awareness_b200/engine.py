@@ -91,6 +91,9 @@ class DecoderEngine:
         self.softcap = getattr(cfg, "final_logit_softcapping", None)
         self.sliding_window = getattr(cfg, "sliding_window", None) if self.is_gemma2 else None
         self.counters = {"k2_launches": 0, "k1_launches": 0}
+        # bench.py sets this to a list to get (start, end) CUDA events around each eager (prompt-pass)
+        # K2 launch, recorded on the launching stream; None = no instrumentation.
+        self.k2_events: Optional[list] = None
 
     # -- masks / positions --------------------------------------------------------------------
     @staticmethod
@@ -168,10 +171,17 @@ class DecoderEngine:
                 nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
                 if not h.is_contiguous():
                     h = h.contiguous()
+                ev = None
+                if self.k2_events is not None and not decode:
+                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                    ev[0].record()
                 y = kernels.inject_rmsnorm(h, nxt.weight, self.eps, self.variant, vtable=steer.vtable,
                                            row_vec=steer.row_vec, row_alpha=steer.row_alpha,
                                            row_t0=None if decode else steer.row_t0, pos0=pos0,
                                            steer_all=decode or steer.row_t0 is None)
+                if ev is not None:
+                    ev[1].record()
+                    self.k2_events.append((ev[0], ev[1], h.numel() * h.element_size()))
                 self.counters["k2_launches"] += 1
                 if i + 1 < self.n_layers:
                     normed_in = y
