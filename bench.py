@@ -141,7 +141,7 @@ def run_ours(args):
     arch = args.arch
     model = build_model(arch, dtype=torch.bfloat16, device=str(dev), seed=None)
     w = ModelWrapper(arch, device=str(dev), dtype=torch.bfloat16, model=model,
-                     tokenizer=StubTokenizer(vocab_size=model.config.vocab_size))
+                     tokenizer=StubTokenizer(vocab_size=model.config.vocab_size), attention=args.attention)
     eng = w.engine
     n_layers = eng.n_layers
     base_layer = get_layer_at_fraction(w, LAYER_FRACTION)
@@ -270,7 +270,7 @@ def run_ours(args):
                 "workload": f"BASELINE configs[1]: {arch} arch, {N_CONCEPTS} concepts x {len(STRENGTHS)} strengths at one "
                             f"layer, one {rows}-row steered batch per GPU, prompt {T_PROMPT} (real {T_MIN}..{T_PROMPT}, "
                             f"left-padded), {N_NEW} greedy tokens, extraction {N_CONCEPTS}+{N_BASE} prompts per step",
-                "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW,
+                "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": args.attention,
                 "parallelism": "independent replicas, layer axis round-robin" if world > 1 else "single replica",
                 "l2": "inputs larger than L2: each step streams 16 GB of weights per decode step and ~1 GB of KV/activations",
             },
@@ -407,6 +407,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--arch", default=ARCH)
     ap.add_argument("--cpu-rows", type=int, default=2)
+    ap.add_argument("--attention", default="gqa", choices=["gqa", "hf"],
+                    help="gqa: grouped-query SDPA without repeat_kv copies; hf: the model's stock attention function")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -26,6 +26,28 @@ import torch
 from . import kernels
 
 
+ATTN_GQA = "ia_b200_gqa_sdpa"
+
+
+def _gqa_sdpa_forward(module, query, key, value, attention_mask, dropout: float = 0.0, scaling=None, **kwargs):
+    """Attention function for HF's registry: torch SDPA with native grouped-query support.
+
+    transformers' stock `sdpa_attention_forward` materialises K and V `num_key_value_groups` times
+    (`repeat_kv`) whenever a mask is present, i.e. for every left-padded batch — at B=200 that is as
+    many bytes per decode step as the model weights.  Same math, K/V read once."""
+    causal = query.shape[2] > 1 and attention_mask is None
+    out = torch.nn.functional.scaled_dot_product_attention(
+        query, key, value, attn_mask=attention_mask, dropout_p=0.0, scale=scaling, is_causal=causal,
+        enable_gqa=key.shape[1] != query.shape[1])
+    return out.transpose(1, 2).contiguous(), None
+
+
+def _register_attention():
+    from transformers import AttentionInterface
+
+    AttentionInterface.register(ATTN_GQA, _gqa_sdpa_forward)
+
+
 @dataclass
 class SteerSpec:
     """Per-row steering for one batch: row b adds alpha[b] * vtable[row_vec[b]] at layer
@@ -67,7 +89,11 @@ class StaticKV:
 class DecoderEngine:
     """Layer loop over a Hugging Face Llama / Qwen2 / Gemma-2 causal LM."""
 
-    def __init__(self, model, fuse_gemma_tail: bool = True):
+    def __init__(self, model, fuse_gemma_tail: bool = True, attention: str = "hf", fused_norms: Optional[bool] = None):
+        """attention: "hf" keeps the model's own attention function (bit-identical to the reference
+        hook path on the same device); "gqa" swaps in `_gqa_sdpa_forward` (no repeat_kv copies).
+        fused_norms: run every RMSNorm of the stack through K2 (one launch instead of torch's ~7
+        eager kernels, same bits); default = on CUDA."""
         self.model = model
         inner = model.model
         if not hasattr(inner, "layers") and hasattr(inner, "language_model"):
@@ -91,6 +117,12 @@ class DecoderEngine:
         self.softcap = getattr(cfg, "final_logit_softcapping", None)
         self.sliding_window = getattr(cfg, "sliding_window", None) if self.is_gemma2 else None
         self.counters = {"k2_launches": 0, "k1_launches": 0}
+        self.fused_norms = (self.device.type == "cuda") if fused_norms is None else fused_norms
+        self.attention = attention
+        if attention == "gqa":
+            _register_attention()
+        elif attention != "hf":
+            raise ValueError(attention)
         # bench.py sets this to a list to get (start, end) CUDA events around each eager (prompt-pass)
         # K2 launch, recorded on the launching stream; None = no instrumentation.
         self.k2_events: Optional[list] = None
@@ -123,10 +155,31 @@ class DecoderEngine:
             out["sliding_attention"] = full & win[None, None]
         return out
 
+    def norm(self, module, x: torch.Tensor) -> torch.Tensor:
+        """An un-steered RMSNorm of the stack: K2 with no rows steered (bit-identical to the eager
+        module for >= 16 row vectors), or the HF module itself."""
+        if self.fused_norms and x.is_cuda and x.dim() == 3:
+            self.counters["k2_launches"] += 1
+            return kernels.inject_rmsnorm(x if x.is_contiguous() else x.contiguous(), module.weight, self.eps, self.variant)
+        return module(x)
+
     # -- the layer loop -----------------------------------------------------------------------
-    def run_layers(self, h: torch.Tensor, pos_emb, masks, cache, steer: Optional[SteerSpec] = None,
-                   pos0: int = 0, decode: bool = False, stop_after: Optional[int] = None,
-                   capture: Optional[Sequence[int]] = None):
+    def run_layers(self, *args, **kwargs):
+        """`_run_layers` with this engine's attention function selected for the duration of the
+        call only, so the HF model object keeps its stock behaviour for anyone else (the parity
+        tests run the reference hook path on the very same model)."""
+        if self.attention != "gqa":
+            return self._run_layers(*args, **kwargs)
+        stock = self.cfg._attn_implementation
+        self.cfg._attn_implementation = ATTN_GQA
+        try:
+            return self._run_layers(*args, **kwargs)
+        finally:
+            self.cfg._attn_implementation = stock
+
+    def _run_layers(self, h: torch.Tensor, pos_emb, masks, cache, steer: Optional[SteerSpec] = None,
+                    pos0: int = 0, decode: bool = False, stop_after: Optional[int] = None,
+                    capture: Optional[Sequence[int]] = None):
         """Runs decoder layers on h [B,T,H].  Returns (final_normed_or_None, captured dict).
         With `stop_after` the loop ends after that layer and nothing is normed."""
         captured: Dict[int, torch.Tensor] = {}
@@ -137,15 +190,15 @@ class DecoderEngine:
         for i in range(last + 1):
             layer = self.layers[i]
             residual = h
-            x = normed_in if normed_in is not None else layer.input_layernorm(h)
+            x = normed_in if normed_in is not None else self.norm(layer.input_layernorm, h)
             normed_in = None
             attn, _ = layer.self_attn(hidden_states=x, position_embeddings=pos_emb,
                                       attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
             steer_here = steer is not None and steer.layer_idx == i
             if self.is_gemma2:
-                h = residual + layer.post_attention_layernorm(attn)
+                h = residual + self.norm(layer.post_attention_layernorm, attn)
                 residual = h
-                m = layer.mlp(layer.pre_feedforward_layernorm(h))
+                m = layer.mlp(self.norm(layer.pre_feedforward_layernorm, h))
                 if steer_here and self.fuse_gemma_tail:
                     nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
                     y = kernels.gemma2_tail_inject_rmsnorm(
@@ -162,11 +215,11 @@ class DecoderEngine:
                     if i in want:
                         captured[i] = h
                     continue
-                h = residual + layer.post_feedforward_layernorm(m)
+                h = residual + self.norm(layer.post_feedforward_layernorm, m)
             else:
                 h = residual + attn
                 residual = h
-                h = residual + layer.mlp(layer.post_attention_layernorm(h))
+                h = residual + layer.mlp(self.norm(layer.post_attention_layernorm, h))
             if steer_here:
                 nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
                 if not h.is_contiguous():
@@ -190,7 +243,7 @@ class DecoderEngine:
             if i in want:
                 captured[i] = h
         if stop_after is None and final is None:
-            final = self.inner.norm(h)
+            final = self.norm(self.inner.norm, h)
         return final, captured
 
     def logits(self, normed_last: torch.Tensor) -> torch.Tensor:

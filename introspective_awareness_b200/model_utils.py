@@ -53,7 +53,8 @@ MODEL_NAME_MAP = {
 
 class ModelWrapper:
     def __init__(self, model_name: str, device: str = "cuda", dtype: torch.dtype = torch.bfloat16,
-                 quantization_config=None, *, model=None, tokenizer=None, compat_slice: bool = False):
+                 quantization_config=None, *, model=None, tokenizer=None, compat_slice: bool = False,
+                 attention: str = "hf"):
         self.model_name = model_name
         self.device = device
         self.dtype = dtype
@@ -73,21 +74,21 @@ class ModelWrapper:
             tokenizer.padding_side = "left"  # reference model_utils.py:97
             if getattr(tokenizer, "pad_token", None) is None:
                 tokenizer.pad_token = tokenizer.eos_token
-        self.engine = DecoderEngine(self.model)
+        self.engine = DecoderEngine(self.model, attention=attention)
         self.n_layers = self.engine.n_layers
         self.hooks: List = []  # kept for interface parity; this runtime registers no hooks
 
     # -- construction helpers -----------------------------------------------------------------
     @classmethod
     def from_arch(cls, arch: str, device: str = "cuda", dtype: torch.dtype = torch.bfloat16, seed: Optional[int] = 0,
-                  tokenizer=None, **overrides) -> "ModelWrapper":
+                  tokenizer=None, attention: str = "hf", **overrides) -> "ModelWrapper":
         """Random-init model of a named architecture + stub tokenizer (offline)."""
         from .stub_tokenizer import StubTokenizer
         from .synthetic import build_model
 
         model = build_model(arch, dtype=dtype, device=device, seed=seed, **overrides)
         tok = tokenizer or StubTokenizer(vocab_size=model.config.vocab_size)
-        return cls(arch, device=device, dtype=dtype, model=model, tokenizer=tok)
+        return cls(arch, device=device, dtype=dtype, model=model, tokenizer=tok, attention=attention)
 
     def _get_input_device(self):
         return next(self.model.parameters()).device

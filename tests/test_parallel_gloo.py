@@ -1,0 +1,92 @@
+"""World-size-2 gloo tests (CPU) of the multi-GPU plumbing: sharding, ragged all-gather,
+all-reduce of partial sums, and the prompt-sharded extraction protocol.  The CUDA kernels are
+replaced by the numpy oracle here (tests may use it); on the GPU box the same protocol runs with
+K1a/K1b (bench.py at --gpus > 1)."""
+
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from introspective_awareness_b200 import parallel
+
+
+def test_sharding_helpers():
+    assert parallel.shard_round_robin(list(range(32)), 3, 8) == [3, 11, 19, 27]
+    assert [parallel.shard_contiguous(50, r, 8) for r in range(8)] == [
+        (0, 7), (7, 14), (14, 20), (20, 26), (26, 32), (32, 38), (38, 44), (44, 50)]
+    assert parallel.shard_contiguous(3, 5, 8) == (3, 3)  # more ranks than items: empty shard
+    cover = []
+    for r in range(5):
+        lo, hi = parallel.shard_contiguous(42, r, 5)
+        cover += list(range(lo, hi))
+    assert cover == list(range(42))  # Gemma-2's 42 layers over 5 ranks: every layer exactly once
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, out_dir):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from oracle import kernels_np as K
+
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    r, w, _ = parallel.init_from_env(backend="gloo")
+    assert (r, w) == (rank, world) and parallel.world() == (rank, world)
+
+    # ragged all-gather along dim 1 and rank-0 gather
+    t = torch.full((2, rank + 1, 3), float(rank))
+    g = parallel.allgather_rows(t, [1, 2], dim=1)
+    assert g.shape == (2, 3, 3) and g[:, 0].eq(0).all() and g[:, 1:].eq(1).all()
+    parts = parallel.gather_to_rank0(torch.tensor([rank * 10 + 1]))
+    assert (parts is None) == (rank != 0)
+    if rank == 0:
+        assert [int(p) for p in parts] == [1, 11]
+
+    # prompt-sharded extraction == single-rank extraction
+    rng = np.random.default_rng(0)
+    L, C, Nb, H = 3, 5, 101, 64
+    conc = K.rd((rng.standard_normal((L, C, H)) * 3 + 5).astype(np.float32), "bf16")
+    base = K.rd((rng.standard_normal((L, Nb, H)) * 3 + 5).astype(np.float32), "bf16")
+
+    def capture_rows_and_sum(segment, lo, hi):
+        src = conc if segment == "concept" else base
+        rows = torch.from_numpy(src[:, lo:hi].copy())
+        sums = torch.from_numpy(np.stack([K.column_sum(src[l, lo:hi]) for l in range(L)]))
+        return rows, sums
+
+    def finalize(rows, base_sum, n_base, mode, normalize):
+        outs = [K.meandiff(rows[l].numpy(), None, "raw" if base_sum is None else mode, "bf16", normalize,
+                           base_sum=None if base_sum is None else base_sum[l].numpy(), n_base=n_base)
+                for l in range(L)]
+        return np.stack([o[1] for o in outs])
+
+    got = parallel.extract_vectors_sharded(capture_rows_and_sum, finalize, C, Nb, "baseline", False)
+    want = np.stack([K.meandiff(conc[l], base[l], "baseline", "bf16")[1] for l in range(L)])
+    rel = np.linalg.norm(got - want, axis=-1) / np.linalg.norm(want, axis=-1)
+    assert rel.max() <= 1e-3, rel.max()
+    # only the fp32 summation order differs (sum of two partial sums): almost every element identical
+    assert (got != want).mean() <= 1e-2
+    raw = parallel.extract_vectors_sharded(capture_rows_and_sum, finalize, C, Nb, "no_baseline", False)
+    assert np.array_equal(raw, conc)
+    np.save(os.path.join(out_dir, f"vec{rank}.npy"), got)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_world_size_2_gloo(tmp_path):
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    a, b = np.load(tmp_path / "vec0.npy"), np.load(tmp_path / "vec1.npy")
+    assert np.array_equal(a, b)  # every rank ends with the same vectors
