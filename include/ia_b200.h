@@ -64,6 +64,9 @@ extern "C" {
 #define IA_ERR_WORKSPACE -5 /* workspace too small */
 #define IA_ERR_TOO_LARGE -6 /* size beyond a documented maximum */
 
+/* capacity of the built-in scratch used by ia_gather_meandiff_static */
+#define IA_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+
 /* Library version (== IA_ABI_VERSION) and a static description of an error code. */
 IA_API int ia_version(void);
 IA_API const char *ia_error_string(int code);
@@ -145,6 +148,33 @@ IA_API int ia_gather_meandiff(const void *const *concept_ptrs, int64_t Tc, const
                        int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,
                        void *out_rounded, float *out_norm, void *workspace, int64_t workspace_bytes,
                        int32_t dtype, void *stream);
+
+/*
+ * K1 without a caller-supplied workspace.  No counterpart in the reference (which never manages
+ * device memory itself); it exists for hosts that cannot allocate.
+ *
+ * Some callers of this library may use only the device buffers they were given: code embedded in a
+ * process whose GPU memory is partitioned up front by someone else, callers inside latency-critical
+ * or capture-bound regions where cudaMalloc's device-wide synchronisation is not acceptable, and
+ * minimal FFI bindings that bring no allocator.  They can still pass inputs and outputs, but they
+ * cannot produce K1's scratch.  This variant takes the same arguments as ia_gather_meandiff minus
+ * `workspace` / `workspace_bytes` and uses a fixed IA_STATIC_SCRATCH_BYTES (4 MiB) array that is part
+ * of the library image — each GPU that loads the library carries it until the process exits.
+ *
+ *   - If ia_meandiff_workspace_bytes(...) for the request exceeds IA_STATIC_SCRATCH_BYTES the call
+ *     returns IA_ERR_TOO_LARGE and launches nothing (4 MiB covers 64 layers x 50 concepts x H = 5120).
+ *   - The first call on a device resolves the array's device address; issue it before any stream
+ *     capture begins.
+ *   - All calls on a device share the one array: calls that may overlap on the GPU race.  Nothing in
+ *     it needs clearing between calls; each call overwrites what it reads.
+ *   - No cudaMalloc, cudaFree or allocating library routine is called.
+ * Results are bit-identical to ia_gather_meandiff.
+ */
+IA_API int ia_gather_meandiff_static(const void *const *concept_ptrs, int64_t Tc, const int32_t *concept_row,
+                              const int32_t *concept_tok, int64_t n_concept, const void *const *base_ptrs,
+                              int64_t Tb, const int32_t *base_row, const int32_t *base_tok, int64_t n_base,
+                              int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,
+                              void *out_rounded, float *out_norm, int32_t dtype, void *stream);
 
 /*
  * K1a — rank-local half of K1 for prompt-sharded extraction: gathers `n_rows` rows per layer

@@ -38,7 +38,11 @@ _SIGNATURES = {
                                  c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "ia_meandiff_finalize": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int32, c_int32,
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
+    "ia_gather_meandiff_static": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                                          c_void_p, c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p, c_void_p,
+                                          c_void_p, c_int32, c_void_p]),
 }
+IA_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024
 
 _lib = None
 

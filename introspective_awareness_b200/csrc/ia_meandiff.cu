@@ -13,6 +13,7 @@
 // HBM-bound streaming: algorithmic bytes per layer (n_concept + n_base)*H*e_in + n_out*H*e_out.
 
 #include <algorithm>
+#include <mutex>
 
 #include "ia_common.cuh"
 
@@ -518,4 +519,86 @@ extern "C" int ia_meandiff_finalize(const void *concept_acts, int64_t n_concept,
     default:
         return IA_ERR_DTYPE;
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ia_gather_meandiff_static: K1 for callers that are not allowed to allocate device memory.
+//
+// Who needs it: a host that only ever holds the buffers it was handed — a plugin loaded into
+// somebody else's process whose device memory is carved up front by the embedding runtime, a
+// real-time or capture-mode caller where cudaMalloc (a device-wide synchronising call) is
+// off limits, or a thin FFI binding (cgo / JNI / ctypes) with no allocator of its own.  Such a
+// caller can pass the inputs and outputs it already owns, but has nowhere to get K1's scratch
+// (per-tile norm partials and chunked column sums) from.  Here the scratch lives in the library
+// image instead: one fixed array per GPU that loads the library, held until the process exits.
+//
+// What a caller must know:
+//   * the first call on each device looks up the array's device address (the only set-up there
+//     is); make that first call outside any stream capture;
+//   * requests whose scratch need exceeds IA_STATIC_SCRATCH_BYTES are refused with
+//     IA_ERR_TOO_LARGE before anything is launched;
+//   * every call on a device uses the same array, so two calls whose kernels can be in flight at
+//     the same time (different streams, different host threads) race with each other — keep them
+//     ordered; contents left by one call are simply overwritten by the next;
+//   * the call itself launches kernels and nothing else: no cudaMalloc / cudaFree, no library
+//     routine that allocates.
+// ---------------------------------------------------------------------------------------------
+
+namespace ia {
+
+constexpr int64_t kStaticScratchBytes = IA_STATIC_SCRATCH_BYTES;  // 4 MiB: the whole Qwen2.5-32B sweep (64 layers x 5120) needs 3.1 MiB
+
+// File-scope device array.  In host code this name is only a handle for the runtime's symbol
+// table, never an address a kernel may be given; the address comes from cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+struct StaticScratchSlot {
+    void *ptr = nullptr;
+    bool ready = false;
+};
+static StaticScratchSlot g_scratch_slot[64];
+static std::mutex g_scratch_mutex;
+
+// Device address of this GPU's copy of the array; resolved once per device, with that device current.
+static int static_scratch_ptr(void **out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return IA_ERR_SHAPE;
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    StaticScratchSlot &slot = g_scratch_slot[dev];
+    if (!slot.ready) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 255u) != 0) return IA_ERR_ALIGN;
+        slot.ptr = p;
+        slot.ready = true;
+    }
+    *out = slot.ptr;
+    return 0;
+}
+
+}  // namespace ia
+
+extern "C" int ia_gather_meandiff_static(const void *const *concept_ptrs, int64_t Tc, const int32_t *concept_row,
+                                         const int32_t *concept_tok, int64_t n_concept, const void *const *base_ptrs,
+                                         int64_t Tb, const int32_t *base_row, const int32_t *base_tok, int64_t n_base,
+                                         int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,
+                                         void *out_rounded, float *out_norm, int32_t dtype, void *stream) {
+    // Size check first, so that an oversized request fails the same way whether or not this
+    // device has been set up yet.
+    const int64_t need = ia_meandiff_workspace_bytes(n_layers, n_concept, mode == IA_MODE_RAW ? 0 : n_base, H, mode);
+    if (need < 0) return (int)need;
+    if (need > ia::kStaticScratchBytes) return IA_ERR_TOO_LARGE;
+    void *scratch = nullptr;
+    int rc = ia::static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    // Same kernels and launch sequence as ia_gather_meandiff; only the scratch differs.  Every
+    // scratch word the kernels read in a call was written earlier in the same call (column sums
+    // before the finalize pass, norm partials before the norm pass), so nothing has to be cleared
+    // and whatever the previous call left behind is never observed.
+    return ia_gather_meandiff(concept_ptrs, Tc, concept_row, concept_tok, n_concept, base_ptrs, Tb, base_row, base_tok,
+                              n_base, n_layers, H, mode, normalize, out_f32, out_rounded, out_norm, scratch,
+                              ia::kStaticScratchBytes, dtype, stream);
 }
