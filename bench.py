@@ -174,8 +174,8 @@ def run_ours(args):
             return vr[0]
         # prompt-sharded: this rank forwards its slice of both prompt sets, for every layer of this step
         uniq = sorted(set(sweep))
-        cl = eng.capture_layers(c_ids[clo:chi], c_mask[clo:chi], uniq)
-        bl = eng.capture_layers(b_ids[blo:bhi], b_mask[blo:bhi], uniq)
+        cl = eng.capture_layers(c_ids[clo:chi], c_mask[clo:chi], uniq, slot=0)
+        bl = eng.capture_layers(b_ids[blo:bhi], b_mask[blo:bhi], uniq, slot=1)
         crow, _ = kernels.gather_segsum(cl, want_rows=True)
         _, bsum = kernels.gather_segsum(bl, want_rows=False)
         parallel.allreduce_sum_(bsum)
@@ -231,7 +231,20 @@ def run_ours(args):
         step_resident()
     sampler = ClockSampler(local) if rank == 0 else None
     eng.k2_events = []
+    if args.ncu_window:
+        # profiler window = the last timed step only (ncu --profile-from-start off -c N)
+        real_step, seen = step_resident, [0]
+
+        def step_resident():  # noqa: F811
+            seen[0] += 1
+            if seen[0] == args.steps:
+                torch.cuda.profiler.start()
+            real_step()
+
     ms_res = timed(step_resident, args.steps)
+    if args.ncu_window:
+        torch.cuda.profiler.stop()
+        step_resident = real_step
     k2_events = eng.k2_events
     eng.k2_events = None
     clocks = sampler.stop() if sampler else None
@@ -410,6 +423,7 @@ def main():
     ap.add_argument("--attention", default="gqa", choices=["gqa", "hf"],
                     help="gqa: grouped-query SDPA without repeat_kv copies; hf: the model's stock attention function")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ncu-window", action="store_true", help="cudaProfilerStart at the last timed step (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -1,9 +1,12 @@
 // K1: fused residual gather + segmented fp32 mean-difference + L2 norm (sm_100a).
 //
-// A lane owns 8 consecutive columns (one 128-bit load of a 16-bit dtype, two of fp32); a warp
-// owns a 256-column tile of one layer.  Rows are gathered straight out of the residual-stream
-// tensors the forward pass produced (pointer table + row/token index), so the captured
-// activations never make a separate trip through HBM or the host.
+// A lane owns 8 consecutive columns (one 128-bit access of a 16-bit dtype, two of fp32); a CTA of
+// 8 warps owns a 256-column tile of one layer.  Rows are gathered straight out of the residual-
+// stream tensors the forward pass produced (pointer table + row/token index), so the captured
+// activations never make a separate trip through HBM or the host.  The rows that feed a column sum
+// are staged into shared memory with cp.async by all 8 warps at once (up to 128 rows = 64 KB in
+// flight per CTA, one memory round trip), then ONE warp adds them in the contractual sequential
+// order out of shared memory; the concept rows are then split over the 8 warps, 4 loads deep.
 //
 // Numeric contract (include/ia_b200.h, oracle/kernels_np.py:meandiff):
 //   column sums: sequential over rows inside chunks of 256 rows, chunk sums added in order;
@@ -92,35 +95,6 @@ template <typename T> struct RowSource {
     }
 };
 
-// Sequential fp32 sum of rows [r0, r1) of `src` for this lane's 8 columns; optionally copies
-// the rows to a compact buffer on the way.
-template <typename T>
-__device__ __forceinline__ void sum_rows(const RowSource<T> &src, int layer, int64_t r0, int64_t r1, int H, int col,
-                                         float (&acc)[8], T *copy_to /* [n, H] for this layer or null */) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-    int64_t r = r0;
-    constexpr int U = 8;
-    for (; r + U <= r1; r += U) {
-        float f[U][8];
-#pragma unroll
-        for (int u = 0; u < U; ++u) load8<T>(src.at(layer, r + u, H) + col, f[u]);
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[u][i]);
-            if (copy_to) store8<T>(copy_to + (r + u) * (int64_t)H + col, f[u]);
-        }
-    }
-    for (; r < r1; ++r) {
-        float f[8];
-        load8<T>(src.at(layer, r, H) + col, f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
-        if (copy_to) store8<T>(copy_to + r * (int64_t)H + col, f);
-    }
-}
-
 struct K1Out {
     float *out_f32;     // [n_layers, n_out, H] or null
     void *out_rounded;  // [n_layers, n_out, H]
@@ -129,84 +103,194 @@ struct K1Out {
     int ntiles;
 };
 
-// Concept rows [c0, c1) step cstep of one (layer, tile): difference against the mean, both
-// roundings, norm partials.
+// Concept rows c0, c0+cstep, ... of one (layer, tile): difference against the mean, both
+// roundings, norm partials.  RB row loads are issued before any store so that RB of them are in
+// flight (the compiler cannot hoist loads above the output stores on its own).
 template <typename T>
 __device__ __forceinline__ void emit_rows(const RowSource<T> &csrc, int layer, int tile, int lane, int H, int col,
                                           bool active, bool raw, const float (&mean32)[8], const float (&meanr)[8],
                                           int64_t c0, int64_t cstep, const K1Out &o) {
+    constexpr int RB = 4;
     const int64_t n_out = csrc.n;
-    for (int64_t c = c0; c < n_out; c += cstep) {
-        float a[8], v32[8], vr[8];
-        if (active) {
-            load8<T>(csrc.at(layer, c, H) + col, a);
-        } else {
+    for (int64_t cb = c0; cb < n_out; cb += cstep * RB) {
+        float a[RB][8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] = 0.f;
+        for (int u = 0; u < RB; ++u) {
+            const int64_t c = cb + u * cstep;
+            if (active && c < n_out) {
+                load8<T>(csrc.at(layer, c, H) + col, a[u]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) a[u][i] = 0.f;
+            }
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            v32[i] = raw ? a[i] : __fsub_rn(a[i], mean32[i]);
-            vr[i] = raw ? a[i] : Elt<T>::rd(__fsub_rn(a[i], meanr[i]));
-        }
-        const int64_t orow = (int64_t)layer * n_out + c;
-        if (active) {
-            if (o.out_f32) store8<float>(o.out_f32 + orow * H + col, v32);
-            store8<T>(static_cast<T *>(o.out_rounded) + orow * H + col, vr);
-        }
-        const float p32 = sq8_warp(v32);
-        const float pr = sq8_warp(vr);
-        if (lane == 0) {
-            o.part32[orow * o.ntiles + tile] = p32;
-            o.partr[orow * o.ntiles + tile] = pr;
+        for (int u = 0; u < RB; ++u) {
+            const int64_t c = cb + u * cstep;
+            if (c >= n_out) break;  // warp-uniform
+            float v32[8], vr[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                v32[i] = raw ? a[u][i] : __fsub_rn(a[u][i], mean32[i]);
+                vr[i] = raw ? a[u][i] : Elt<T>::rd(__fsub_rn(a[u][i], meanr[i]));
+            }
+            const int64_t orow = (int64_t)layer * n_out + c;
+            if (active) {
+                if (o.out_f32) store8<float>(o.out_f32 + orow * H + col, v32);
+                store8<T>(static_cast<T *>(o.out_rounded) + orow * H + col, vr);
+            }
+            const float p32 = sq8_warp(v32);
+            const float pr = sq8_warp(vr);
+            if (lane == 0) {
+                o.part32[orow * o.ntiles + tile] = p32;
+                o.partr[orow * o.ntiles + tile] = pr;
+            }
         }
     }
 }
 
-// Fused path: n_base <= 256 (or RAW).  One warp per (layer, tile).
+// ---- CTA-cooperative column sum ---------------------------------------------------------------
+constexpr int kStageBytes = 64 * 1024;  // shared-memory staging buffer for baseline rows
+constexpr int kMeanBytes = 2 * kTileCols * (int)sizeof(float);
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_drain() {
+    asm volatile("cp.async.commit_group;\n" ::);
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+template <typename T> __device__ __forceinline__ void lds8(const unsigned char *p, float (&f)[8]);
+template <> __device__ __forceinline__ void lds8<__nv_bfloat16>(const unsigned char *p, float (&f)[8]) {
+    const uint4 r = *reinterpret_cast<const uint4 *>(p);
+    f[0] = __uint_as_float(r.x << 16); f[1] = __uint_as_float(r.x & 0xffff0000u);
+    f[2] = __uint_as_float(r.y << 16); f[3] = __uint_as_float(r.y & 0xffff0000u);
+    f[4] = __uint_as_float(r.z << 16); f[5] = __uint_as_float(r.z & 0xffff0000u);
+    f[6] = __uint_as_float(r.w << 16); f[7] = __uint_as_float(r.w & 0xffff0000u);
+}
+template <> __device__ __forceinline__ void lds8<__half>(const unsigned char *p, float (&f)[8]) {
+    const uint4 r = *reinterpret_cast<const uint4 *>(p);
+    const __half2 *h = reinterpret_cast<const __half2 *>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { f[2 * i] = __low2float(h[i]); f[2 * i + 1] = __high2float(h[i]); }
+}
+template <> __device__ __forceinline__ void lds8<float>(const unsigned char *p, float (&f)[8]) {
+    const float4 a = reinterpret_cast<const float4 *>(p)[0], b = reinterpret_cast<const float4 *>(p)[1];
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+// Sequential fp32 column sum of rows [r0, r1) for this CTA's tile.  All warps stage rows into
+// `stage` (cp.async, kStageBytes / row bytes rows per pass); warp 0 then adds them in row order.
+// On return warp 0 holds the sums for columns col..col+7 in acc[]; other warps hold zeros.
+// With copy_to, the staged rows are also written out compactly (all warps, 16-byte stores).
 template <typename T>
-__global__ void __launch_bounds__(128) k1_fused_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
+__device__ __forceinline__ void cta_column_sum(const RowSource<T> &src, int layer, int64_t r0, int64_t r1, int H, int col,
+                                               bool active, unsigned char *stage, float (&acc)[8], T *copy_to) {
+    constexpr int kRowBytes = kTileCols * (int)sizeof(T);
+    constexpr int kPassRows = kStageBytes / kRowBytes;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    for (int64_t p0 = r0; p0 < r1; p0 += kPassRows) {
+        const int n = (int)((r1 - p0) < kPassRows ? (r1 - p0) : kPassRows);
+        if (active) {
+            for (int r = warp; r < n; r += nwarps) {
+                const T *g = src.at(layer, p0 + r, H) + col;
+                unsigned char *d = stage + (size_t)r * kRowBytes + lane * 8 * sizeof(T);
+                cp_async16(d, g);
+                if (sizeof(T) == 4) cp_async16(d + 16, g + 4);
+            }
+        }
+        cp_async_drain();
+        __syncthreads();
+        if (warp == 0 && active) {
+            const unsigned char *base = stage + lane * 8 * sizeof(T);
+            int r = 0;
+            for (; r + 8 <= n; r += 8) {
+                float f[8][8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) lds8<T>(base + (size_t)(r + u) * kRowBytes, f[u]);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[u][i]);
+                }
+            }
+            for (; r < n; ++r) {
+                float f[8];
+                lds8<T>(base + (size_t)r * kRowBytes, f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+            }
+        }
+        if (copy_to && active) {
+            for (int r = warp; r < n; r += nwarps) {
+                const unsigned char *sp = stage + (size_t)r * kRowBytes + lane * 8 * sizeof(T);
+                unsigned char *dp = reinterpret_cast<unsigned char *>(copy_to + (p0 + r) * (int64_t)H + col);
+                *reinterpret_cast<uint4 *>(dp) = *reinterpret_cast<const uint4 *>(sp);
+                if (sizeof(T) == 4) *reinterpret_cast<uint4 *>(dp + 16) = *reinterpret_cast<const uint4 *>(sp + 16);
+            }
+        }
+        __syncthreads();  // the stage is overwritten by the next pass
+    }
+}
+
+// Fused path: n_base <= 256 (or RAW).  One CTA (8 warps) per (layer, tile).
+template <typename T>
+__global__ void __launch_bounds__(256) k1_fused_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
                                                        K1Out o) {
-    const int lane = threadIdx.x & 31;
-    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (w >= n_layers * o.ntiles) return;
-    const int layer = w / o.ntiles;
-    const int tile = w - layer * o.ntiles;
+    extern __shared__ __align__(16) unsigned char smem[];
+    float *mean_s = reinterpret_cast<float *>(smem);  // [2][kTileCols]: fp32 mean, rounded mean
+    unsigned char *stage = smem + kMeanBytes;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int layer = blockIdx.x / o.ntiles;
+    const int tile = blockIdx.x - layer * o.ntiles;
     const int col = tile * kTileCols + lane * 8;
     const bool active = col < H;
     float mean32[8], meanr[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) { mean32[i] = 0.f; meanr[i] = 0.f; }
-    if (!raw && active) {
+    if (!raw) {
         float acc[8];
-        sum_rows<T>(bsrc, layer, 0, bsrc.n, H, col, acc, nullptr);
-        const float nb = (float)bsrc.n;
+        cta_column_sum<T>(bsrc, layer, 0, bsrc.n, H, col, active, stage, acc, nullptr);
+        if (warp == 0) {
+            const float nb = (float)bsrc.n;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float m = active ? __fdiv_rn(acc[i], nb) : 0.f;
+                mean_s[lane * 8 + i] = m;
+                mean_s[kTileCols + lane * 8 + i] = Elt<T>::rd(m);
+            }
+        }
+        __syncthreads();
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            mean32[i] = __fdiv_rn(acc[i], nb);
-            meanr[i] = Elt<T>::rd(mean32[i]);
+            mean32[i] = mean_s[lane * 8 + i];
+            meanr[i] = mean_s[kTileCols + lane * 8 + i];
         }
     }
-    emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, 0, 1, o);
+    emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, warp, nwarps, o);
 }
 
-// Chunked column sums: one warp per (chunk, layer, tile); also the rank-local gather.
+// Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.
 template <typename T>
-__global__ void __launch_bounds__(128) k1_segsum_kernel(RowSource<T> src, int n_layers, int H, int ntiles, int nchunks,
+__global__ void __launch_bounds__(256) k1_segsum_kernel(RowSource<T> src, int n_layers, int H, int ntiles, int nchunks,
                                                         float *part /* [nchunks, n_layers, H] */, T *copy_to) {
-    const int lane = threadIdx.x & 31;
-    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (w >= (int64_t)nchunks * n_layers * ntiles) return;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t w = blockIdx.x;
     const int tile = (int)(w % ntiles);
     const int layer = (int)((w / ntiles) % n_layers);
     const int chunk = (int)(w / ((int64_t)ntiles * n_layers));
     const int col = tile * kTileCols + lane * 8;
-    if (col >= H) return;
+    const bool active = col < H;
     const int64_t r0 = (int64_t)chunk * kChunkRows;
     const int64_t r1 = r0 + kChunkRows < src.n ? r0 + kChunkRows : src.n;
     float acc[8];
-    sum_rows<T>(src, layer, r0, r1, H, col, acc, copy_to ? copy_to + (int64_t)layer * src.n * H : nullptr);
-    store8<float>(part + ((int64_t)chunk * n_layers + layer) * H + col, acc);
+    cta_column_sum<T>(src, layer, r0, r1, H, col, active, smem, acc, copy_to ? copy_to + (int64_t)layer * src.n * H : nullptr);
+    if (warp == 0 && active) store8<float>(part + ((int64_t)chunk * n_layers + layer) * H + col, acc);
 }
 
 // out[l, :] = part[0, l, :] + part[1, l, :] + ... in ascending chunk order.
@@ -344,10 +428,12 @@ static int run_segsum(const RowSource<T> &src, int L, int H, float *part, float 
     const int ntiles = (H + kTileCols - 1) / kTileCols;
     const int nch = nchunks_of(src.n);
     if (src.n == 0) return (int)cudaMemsetAsync(sum_out, 0, sizeof(float) * (size_t)L * H, s);
-    const int64_t warps = (int64_t)nch * L * ntiles;
+    const int64_t ctas = (int64_t)nch * L * ntiles;
     float *dst = nch == 1 ? sum_out : part;
-    k1_segsum_kernel<T><<<(unsigned)((warps + 3) / 4), 128, 0, s>>>(src, L, H, ntiles, nch, dst, copy_to);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = cudaFuncSetAttribute(k1_segsum_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);
+    if (e != cudaSuccess) return (int)e;
+    k1_segsum_kernel<T><<<(unsigned)ctas, 256, kStageBytes, s>>>(src, L, H, ntiles, nch, dst, copy_to);
+    e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
     if (nch > 1) {
         const int64_t per = (int64_t)L * H;
@@ -388,9 +474,11 @@ static int gather_meandiff_t(const void *const *cptrs, int64_t Tc, const int32_t
     K1Out o{out_f32, out_rounded, ws + wl.part32, ws + wl.partr, ntiles};
     const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : nc;
     if (mode != IA_MODE_POSNEG && (mode == IA_MODE_RAW || nb <= kChunkRows)) {
-        const int warps = L * ntiles;
-        k1_fused_kernel<T><<<(unsigned)((warps + 3) / 4), 128, 0, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, o);
-        cudaError_t e = cudaGetLastError();
+        const int smem = kMeanBytes + (mode == IA_MODE_RAW ? 0 : kStageBytes);
+        cudaError_t e = cudaFuncSetAttribute(k1_fused_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMeanBytes + kStageBytes);
+        if (e != cudaSuccess) return (int)e;
+        k1_fused_kernel<T><<<(unsigned)(L * ntiles), 256, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, o);
+        e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         const int64_t rows = (int64_t)L * n_out;
         k1_norm_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(rows, H, normalize, out_norm, o);

@@ -118,6 +118,8 @@ class DecoderEngine:
         self.sliding_window = getattr(cfg, "sliding_window", None) if self.is_gemma2 else None
         self.counters = {"k2_launches": 0, "k1_launches": 0}
         self.fused_norms = (self.device.type == "cuda") if fused_norms is None else fused_norms
+        self.graph_extraction = True
+        self._extract_graphs: Dict[tuple, tuple] = {}
         self.attention = attention
         if attention == "gqa":
             _register_attention()
@@ -138,18 +140,20 @@ class DecoderEngine:
         kinds = getattr(self.cfg, "layer_types", None)
         return kinds[i] if kinds else "full_attention"
 
-    def prefill_masks(self, attention_mask: torch.Tensor) -> Dict[str, Optional[torch.Tensor]]:
+    def prefill_masks(self, attention_mask: torch.Tensor, padded: Optional[bool] = None) -> Dict[str, Optional[torch.Tensor]]:
         """4-D boolean masks [B,1,T,T] (True = attend): causal AND key-not-padding, plus the window
-        for Gemma-2 sliding layers.  None when nothing is padded (SDPA then runs is_causal)."""
+        for Gemma-2 sliding layers.  None when nothing is padded (SDPA then runs is_causal).
+        `padded` may be given by a caller that already knows (avoids a host sync, e.g. under capture)."""
         b, t = attention_mask.shape
         valid = attention_mask.bool()
         need_window = self.sliding_window is not None and t > self.sliding_window
-        if bool(valid.all()) and not need_window:
+        all_valid = bool(valid.all()) if padded is None else not padded
+        if all_valid and not need_window:
             return {"full_attention": None, "sliding_attention": None}
         q = torch.arange(t, device=attention_mask.device)
         causal = q[None, :] <= q[:, None]
         full = (causal[None, None] & valid[:, None, None, :])
-        out = {"full_attention": None if bool(valid.all()) else full, "sliding_attention": None if bool(valid.all()) else full}
+        out = {"full_attention": None if all_valid else full, "sliding_attention": None if all_valid else full}
         if need_window:
             win = (q[:, None] - q[None, :]) < self.sliding_window
             out["sliding_attention"] = full & win[None, None]
@@ -256,7 +260,7 @@ class DecoderEngine:
     # -- extraction ---------------------------------------------------------------------------
     @torch.inference_mode()
     def capture_layers(self, input_ids: torch.Tensor, attention_mask: torch.Tensor,
-                       layer_indices: Sequence[int]) -> List[torch.Tensor]:
+                       layer_indices: Sequence[int], slot: int = 0) -> List[torch.Tensor]:
         """One forward, stopped after the deepest requested layer; returns the residual stream
         [B,T,H] after each requested layer (reference model_utils.py:312-338 runs the whole model,
         once per layer)."""
@@ -264,14 +268,51 @@ class DecoderEngine:
         for i in layer_indices:
             if not 0 <= i < self.n_layers:
                 raise IndexError(f"layer {i} out of range")
-        ids = input_ids.to(self.device)
-        mask = attention_mask.to(self.device)
+        padded = not bool(attention_mask.all())
+        if self.device.type == "cuda" and self.graph_extraction:
+            return self._capture_layers_graphed(input_ids, attention_mask, layer_indices, padded, slot)
+        return self._capture_layers_eager(input_ids.to(self.device), attention_mask.to(self.device), layer_indices, padded)
+
+    def _capture_layers_eager(self, ids, mask, layer_indices, padded):
         h = self.inner.embed_tokens(ids)
         pos = self.position_ids(mask)
         pos_emb = self.inner.rotary_emb(h, pos)
-        _, got = self.run_layers(h, pos_emb, self.prefill_masks(mask), None, stop_after=max(layer_indices),
+        _, got = self.run_layers(h, pos_emb, self.prefill_masks(mask, padded), None, stop_after=max(layer_indices),
                                  capture=layer_indices)
         return [got[i] for i in layer_indices]
+
+    def _capture_layers_graphed(self, input_ids, attention_mask, layer_indices, padded, slot):
+        """The extraction forward is ~1500 small launches (short prompts), i.e. CPU-launch-bound when
+        run eagerly: replay it as one CUDA graph per (batch, width, layers) shape.  The returned
+        tensors live in the graph's pool and are overwritten by the next replay of the same shape and
+        `slot` (callers that need two captures alive at once, e.g. concept and baseline batches, use
+        different slots)."""
+        key = (tuple(input_ids.shape), tuple(layer_indices), padded, slot)
+        entry = self._extract_graphs.get(key)
+        if entry is None:
+            if len(self._extract_graphs) >= 8:
+                self._extract_graphs.clear()
+            ids_s = torch.zeros(input_ids.shape, dtype=torch.long, device=self.device)
+            mask_s = torch.ones(attention_mask.shape, dtype=torch.long, device=self.device)
+            ids_s.copy_(input_ids)
+            mask_s.copy_(attention_mask)
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    self._capture_layers_eager(ids_s, mask_s, layer_indices, padded)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                outs = self._capture_layers_eager(ids_s, mask_s, layer_indices, padded)
+            entry = (g, ids_s, mask_s, outs)
+            self._extract_graphs[key] = entry
+        g, ids_s, mask_s, outs = entry
+        ids_s.copy_(input_ids, non_blocking=True)
+        mask_s.copy_(attention_mask, non_blocking=True)
+        g.replay()
+        return outs
 
     @torch.inference_mode()
     def extract_vectors(self, concept_ids, concept_mask, base_ids, base_mask, layer_indices: Sequence[int],
@@ -282,10 +323,10 @@ class DecoderEngine:
         each [n_layers, n_out, H] / [n_layers, n_out]."""
         if not self.device.type == "cuda":
             raise RuntimeError("concept-vector extraction needs the CUDA kernels; there is no CPU path")
-        cl = self.capture_layers(concept_ids, concept_mask, layer_indices)
+        cl = self.capture_layers(concept_ids, concept_mask, layer_indices, slot=0)
         bl = None
         if mode not in ("no_baseline", "raw"):
-            bl = self.capture_layers(base_ids, base_mask, layer_indices)
+            bl = self.capture_layers(base_ids, base_mask, layer_indices, slot=1)
 
         def tok(t_len, n):
             t = token_idx if token_idx >= 0 else t_len + token_idx  # reference slices the padded tensor

@@ -107,9 +107,15 @@ def main():
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--impl", default="regs")
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--only-rows", type=int, default=0, help="run a single cold K2 shape (for ncu --set full)")
     args = ap.parse_args()
     peak, src = peak_gbs()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda:0")
+    if args.only_rows:
+        r = bench_k2(args.only_rows, 1, 4096, "llama", args.impl, args.reps, flush)
+        r.update(cache="cold", frac=r["gbs"] / peak, peak=peak, peak_src=src)
+        print(json.dumps(r), flush=True)
+        return
     rows_ladder = [200, 3000, 25600] if args.quick else [200, 3000, 25600, 262144]
     hs = [4096] if args.quick else [896, 3584, 4096, 5120]
     for H in hs:
