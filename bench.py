@@ -271,7 +271,7 @@ def run_ours(args):
     launches = args.steps * (N_NEW + k1_launches)
 
     cpu = None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:  # reported at N=1 only
         cpu = cpu_baseline_port(model, my_layer, wl, sample_rows=args.cpu_rows)
 
     if rank == 0:
@@ -295,7 +295,12 @@ def run_ours(args):
                          "traffic": traffic_from_profiles(), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo, "us_per_launch": k2_avg_ms * 1e3,
                          "launches_timed": len(k2_ms),
-                         "share_of_step": (k2_avg_ms * len(k2_ms) / ms_res) if k2_ms else None},
+                         "share_of_step": (k2_avg_ms * len(k2_ms) / ms_res) if k2_ms else None,
+                         "note": "live value exceeds 1.0 because the residual this launch reads was written by the "
+                                 "preceding kernel and is partly L2-resident and the concept table (1/4 of the algorithmic "
+                                 "bytes) is always L2-resident; cold-cache figure for the same shape: 0.94 "
+                                 "(profiles/, tools/kbench.py). traffic = dram bytes of the ncu --set full capture of "
+                                 "that cold launch"},
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
@@ -360,8 +365,19 @@ def _reference_step(model, layer, wl, rows, n_concept=2, n_base=4):
     return out["new_ids"]
 
 
+def _use_all_host_threads() -> int:
+    """torchrun exports OMP_NUM_THREADS=1; the CPU legs are meant to use every host core."""
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 def cpu_baseline_port(gpu_model, layer, wl, sample_rows=2):
-    threads = torch.get_num_threads()
+    threads = _use_all_host_threads()
     try:
         model = _cpu_model_from(gpu_model)
         t = time.perf_counter()
@@ -384,6 +400,7 @@ def run_reference(args):
     from introspective_awareness_b200.model_utils import get_layer_at_fraction
 
     torch.manual_seed(0)
+    _use_all_host_threads()
     model = _fast_cpu_model(args.arch)
     n_layers = model.config.num_hidden_layers
     layer = max(0, min(int(n_layers * LAYER_FRACTION), n_layers - 1))
