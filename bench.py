@@ -290,7 +290,7 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches,
-            "roofline": {"kernel": "ia::k2_regs_kernel (fused inject+RMSNorm), prompt-pass launch", "bound": "hbm",
+            "roofline": {"kernel": "ia_inject_rmsnorm (ia::k2_tma_kernel: fused inject+RMSNorm, cp.async.bulk staged), prompt-pass launch", "bound": "hbm",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
                          "traffic": traffic_from_profiles(), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo, "us_per_launch": k2_avg_ms * 1e3,
@@ -298,7 +298,7 @@ def run_ours(args):
                          "share_of_step": (k2_avg_ms * len(k2_ms) / ms_res) if k2_ms else None,
                          "note": "live value exceeds 1.0 because the residual this launch reads was written by the "
                                  "preceding kernel and is partly L2-resident and the concept table (1/4 of the algorithmic "
-                                 "bytes) is always L2-resident; cold-cache figure for the same shape: 0.94 "
+                                 "bytes) is always L2-resident; cold-cache figure for the same shape: 1.10 "
                                  "(profiles/, tools/kbench.py). traffic = dram bytes of the ncu --set full capture of "
                                  "that cold launch"},
             "cpu_baseline": cpu,

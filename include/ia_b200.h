@@ -48,7 +48,9 @@ extern "C" {
 /* ia_inject_rmsnorm `flags` */
 #define IA_STEER_ALL 1   /* ignore row_t0: steer every position (decode steps; positions=None) */
 #define IA_RSQRT_IEEE 2  /* r = 1/sqrt(.) with IEEE div+sqrt (torch CPU) instead of rsqrtf (torch CUDA) */
-#define IA_IMPL_TMA 4    /* use the bulk-copy (TMA) staged implementation instead of the register one */
+#define IA_IMPL_TMA 4    /* force the bulk-copy (TMA, cp.async.bulk + mbarrier) staged implementation */
+#define IA_IMPL_REGS 8   /* force the register-resident implementation */
+/* neither bit: automatic — TMA staging when a row is >= 4 KiB and the table is in the model dtype */
 
 /* extraction methods (ia_gather_meandiff / ia_meandiff_finalize `mode`) */
 #define IA_MODE_BASELINE 0 /* v_c = act_c - mean_b(act_b)      vector_utils.py:541-545           */

@@ -15,101 +15,31 @@
 // Every product and sum that torch rounds separately is issued as __fmul_rn/__fadd_rn so the
 // compiler cannot contract them into an FMA.
 
-#include "ia_common.cuh"
+#include "ia_k2_common.cuh"
 
 namespace ia {
 
-struct K2Params {
-    void *h;            // [nvec, H] in/out (TAIL: residual in/out)
-    void *y;            // [nvec, H] out
-    const void *mlp;    // TAIL only: [nvec, H] MLP output
-    const void *vtable; // [n_vec, H]
-    const int32_t *row_vec;
-    const float *row_alpha;
-    const int32_t *row_t0;
-    const void *w;      // next norm weight [H]
-    const void *w_post; // TAIL only: post-feedforward norm weight [H]
-    float eps;
-    float inv_h;
-    int nvec;  // rows * T
-    int T;
-    int H;
-    int pos0;
-    int steer_all;
-};
-
-template <bool IEEE> __device__ __forceinline__ float rinv(float var, float eps) {
-    float t = __fadd_rn(var, eps);
-    if (IEEE) return __fdiv_rn(1.0f, __fsqrt_rn(t));
-    return rsqrtf(t);
-}
-
-__device__ __forceinline__ float warp_total(float a0, float a1, float a2, float a3) {
-    float s = __fadd_rn(__fadd_rn(__fadd_rn(a0, a1), a2), a3);
+// Injects one table row into the register-resident vector and stores h'.  The h' stores may alias
+// the table as far as the compiler knows, so it will not hoist table loads above them: VB loads
+// are issued explicitly before the stores they precede, keeping VB of them in flight.
+template <typename T, typename VT, int MAXJ>
+__device__ __forceinline__ void inject_row_regs(Pack4<T> (&x)[MAXJ], const Injector<T, VT> &inj, const VT *vp, T *hp,
+                                                int lane, int nj) {
+    constexpr int VB = sizeof(VT) == 4 ? 4 : 8;  // 16 registers of table data in flight per lane
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) s = __fadd_rn(s, __shfl_down_sync(FULL, s, off));
-    return __shfl_sync(FULL, s, 0);
-}
-
-template <typename T, int VARIANT> __device__ __forceinline__ float norm_out(float x, float r, float w) {
-    float n = __fmul_rn(x, r);
-    if (VARIANT == IA_NORM_LLAMA) return Elt<T>::rd(__fmul_rn(w, Elt<T>::rd(n)));
-    return Elt<T>::rd(__fmul_rn(n, __fadd_rn(1.0f, w)));
-}
-
-// cp.async (LDGSTS) of one 4-element group: asynchronous, no register staging.
-template <int BYTES> __device__ __forceinline__ void cp_async_group(void *smem_dst, const void *gsrc) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;\n" ::"r"(d), "l"(gsrc), "n"(BYTES));
-}
-__device__ __forceinline__ void cp_async_wait_all() {
-    asm volatile("cp.async.commit_group;\n" ::);
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-}
-
-template <typename T>
-__device__ __forceinline__ void sumsq4(const Pack4<T> &x, float &a0, float &a1, float &a2, float &a3) {
-    float f[4];
-    Elt<T>::unpack(x, f);
-    a0 = __fadd_rn(a0, __fmul_rn(f[0], f[0]));
-    a1 = __fadd_rn(a1, __fmul_rn(f[1], f[1]));
-    a2 = __fadd_rn(a2, __fmul_rn(f[2], f[2]));
-    a3 = __fadd_rn(a3, __fmul_rn(f[3], f[3]));
-}
-
-// y group = norm(x group): LLAMA rounds x*r to the dtype before the weight multiply.
-template <typename T, int VARIANT>
-__device__ __forceinline__ void norm4(const Pack4<T> &x, float r, const Pack4<T> &w, Pack4<T> &out) {
-    float f[4], wf[4];
-    Elt<T>::unpack(x, f);
-    Elt<T>::unpack(w, wf);
+    for (int j0 = 0; j0 < MAXJ; j0 += VB) {
+        Pack4<VT> vv[VB];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) f[i] = __fmul_rn(f[i], r);
-    if (VARIANT == IA_NORM_LLAMA) {
-        Pack4<T> tmp;
-        Elt<T>::rd4(f, tmp);
+        for (int jj = 0; jj < VB; ++jj)
+            if (j0 + jj < MAXJ && j0 + jj < nj) vv[jj] = ld4_ro<VT>(vp + 4 * (lane + 32 * (j0 + jj)));
 #pragma unroll
-        for (int i = 0; i < 4; ++i) f[i] = __fmul_rn(wf[i], f[i]);
-    } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) f[i] = __fmul_rn(f[i], __fadd_rn(1.0f, wf[i]));
+        for (int jj = 0; jj < VB; ++jj) {
+            if (j0 + jj < MAXJ && j0 + jj < nj) {
+                inj.apply(x[j0 + jj], vv[jj]);
+                st4<T>(hp + 4 * (lane + 32 * (j0 + jj)), x[j0 + jj]);
+            }
+        }
     }
-    Elt<T>::rd4(f, out);
-}
-
-// x group += round(v group * alpha), rounded to the dtype.
-template <typename T, typename VT>
-__device__ __forceinline__ void inject4(Pack4<T> &x, const Pack4<VT> &v, float alpha) {
-    float f[4], vf[4];
-    Elt<T>::unpack(x, f);
-    Elt<VT>::unpack(v, vf);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) vf[i] = __fmul_rn(vf[i], alpha);
-    Pack4<T> tmp;
-    Elt<T>::rd4(vf, tmp);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) f[i] = __fadd_rn(f[i], vf[i]);
-    Elt<T>::rd4(f, x);
 }
 
 // Register-resident implementation: MAXJ = groups of 4 elements per lane; requires H % 128 == 0
@@ -180,24 +110,9 @@ __global__ void __launch_bounds__(128, MINB) k2_regs_kernel(const K2Params p) {
         }
 
         if (steer) {
-            // The h' stores may alias the table as far as the compiler knows, so it will not hoist
-            // table loads above them: batch VB loads explicitly to keep VB of them in flight.
             const VT *vp = static_cast<const VT *>(p.vtable) + (size_t)vi * H;
-            constexpr int VB = sizeof(VT) == 4 ? 4 : 8;  // 16 registers of table data in flight per lane
-#pragma unroll
-            for (int j0 = 0; j0 < MAXJ; j0 += VB) {
-                Pack4<VT> vv[VB];
-#pragma unroll
-                for (int jj = 0; jj < VB; ++jj)
-                    if (j0 + jj < MAXJ && j0 + jj < nj) vv[jj] = ld4_ro<VT>(vp + 4 * (lane + 32 * (j0 + jj)));
-#pragma unroll
-                for (int jj = 0; jj < VB; ++jj) {
-                    if (j0 + jj < MAXJ && j0 + jj < nj) {
-                        inject4<T, VT>(x[j0 + jj], vv[jj], alpha);
-                        st4<T>(hp + 4 * (lane + 32 * (j0 + jj)), x[j0 + jj]);
-                    }
-                }
-            }
+            const Injector<T, VT> inj(alpha);
+            inject_row_regs<T, VT, MAXJ>(x, inj, vp, hp, lane, nj);
         } else if (TAIL) {
 #pragma unroll
             for (int j = 0; j < MAXJ; ++j)
@@ -248,11 +163,12 @@ __global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
         const bool steer = vi >= 0 && (p.steer_all || (pos + p.pos0 >= t0));
         T *hp = hbase + (size_t)vec * H;
         const VT *vp = static_cast<const VT *>(p.vtable) + (size_t)(steer ? vi : 0) * H;
+        const Injector<T, VT> inj(alpha);
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         for (int g = lane; g < G; g += 32) {
             Pack4<T> x = ld4<T>(hp + 4 * g);
             if (steer) {
-                inject4<T, VT>(x, ld4_ro<VT>(vp + 4 * g), alpha);
+                inj.apply(x, ld4_ro<VT>(vp + 4 * g));
                 st4<T>(hp + 4 * g, x);
             }
             sumsq4<T>(x, a0, a1, a2, a3);
@@ -267,7 +183,7 @@ __global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
     }
 }
 
-static int sm_count() {
+int sm_count() {
     static int cached[64] = {0};
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
@@ -373,6 +289,16 @@ extern "C" int ia_inject_rmsnorm(void *h, void *y, const void *vtable, const int
     p.h = h; p.y = y; p.mlp = nullptr; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
     p.row_t0 = row_t0; p.w = w; p.w_post = nullptr; p.eps = eps; p.inv_h = 1.0f / (float)H;
     p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
+    // Implementation choice (same bits either way): bulk-copy staging wins once a row is a few KiB
+    // (measured on B200: 1.10 vs 0.95 of the copy-bandwidth peak at H = 4096); short rows make its
+    // per-row barrier/issue overhead visible, so they stay on the register kernel.
+    const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
+    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 5 + 1024 <= 220 * 1024;
+    const bool want_tma = (flags & IA_IMPL_TMA) || (!(flags & IA_IMPL_REGS) && row_bytes >= 4096);
+    if (flags & IA_IMPL_TMA) {
+        if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
+    }
+    if (want_tma && tma_ok) return launch_k2_tma(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
     return dispatch_dtype<false>(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
 }
 

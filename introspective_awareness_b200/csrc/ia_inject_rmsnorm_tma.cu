@@ -1,0 +1,203 @@
+// K2, bulk-copy (TMA) staged implementation for sm_100a — selected with IA_IMPL_TMA.
+//
+// Same arithmetic, same summation order, same bits as the register kernel; what changes is how
+// the bytes arrive.  Each warp owns a two-stage ring in shared memory.  One lane issues
+// `cp.async.bulk` (the TMA engine; SASS UBLKCP) for the NEXT vector's residual row and, when that
+// vector is steered, its concept-table row, completing on a per-stage mbarrier, while the whole
+// warp works on the CURRENT vector out of shared memory.  DRAM and L2 latency are therefore off
+// the critical path and no registers are tied up by loads in flight; the row lives in shared memory
+// (h' is written back in place for the second pass), so the kernel is not templated on H.
+//
+// One persistent CTA per SM; warps per CTA = what 2 stages x (row + table row) fit in 220 KB.
+// Outputs leave through ordinary 64-bit stores (fire-and-forget; they never stall the warp).
+
+#include "ia_k2_common.cuh"
+
+namespace ia {
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(void *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(void *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, unsigned bytes, void *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+
+struct RowMeta {
+    int vi;
+    float alpha;
+    bool steer;
+};
+
+template <typename T> __device__ __forceinline__ RowMeta load_meta(const K2Params &p, int vec) {
+    RowMeta m;
+    const int row = vec / p.T;
+    const int pos = vec - row * p.T;
+    m.vi = p.row_vec ? __ldg(p.row_vec + row) : -1;
+    const int t0 = (p.row_vec && !p.steer_all) ? __ldg(p.row_t0 + row) : 0;
+    m.alpha = p.row_vec ? __ldg(p.row_alpha + row) : 0.0f;
+    m.steer = m.vi >= 0 && (p.steer_all || (pos + p.pos0 >= t0));
+    return m;
+}
+
+template <typename T, int VARIANT, bool IEEE>
+__global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    constexpr int S = 2;  // stages per warp: one being consumed, one being filled
+    const int H = p.H;
+    const int G = H >> 2;
+    const unsigned row_bytes = (unsigned)H * sizeof(T);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    // layout: [weight row][mbarriers: nwarps*S x 8 B, padded to 128][stages: nwarps x S x (h row + v row)]
+    T *w_s = reinterpret_cast<T *>(smem);
+    const unsigned bars_off = (row_bytes + 127u) & ~127u;
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem + bars_off) + warp * S;
+    const unsigned stage_off = bars_off + ((unsigned)(nwarps * S * 8 + 127) & ~127u);
+    unsigned char *my_stage = smem + stage_off + (size_t)warp * S * 2 * row_bytes;
+
+    for (int g = threadIdx.x; g < G; g += blockDim.x)
+        cp_async_group<sizeof(Pack4<T>)>(w_s + 4 * g, static_cast<const T *>(p.w) + 4 * g);
+    if (lane == 0) {
+        for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
+        fence_proxy_async();  // make the initialised barriers visible to the async (TMA) proxy
+    }
+    __syncwarp();
+
+    T *hbase = static_cast<T *>(p.h);
+    T *ybase = static_cast<T *>(p.y);
+    const T *vtab = static_cast<const T *>(p.vtable);
+    const int stride = gridDim.x * nwarps;
+    int vec = blockIdx.x * nwarps + warp;
+
+    auto issue = [&](int stage, int v, const RowMeta &m) {
+        // one lane: arm the barrier with the byte count, then start the bulk copies
+        if (lane == 0) {
+            unsigned char *dst = my_stage + (size_t)stage * 2 * row_bytes;
+            fence_proxy_async();  // earlier generic-proxy accesses to this stage are done (warp synced)
+            mbar_expect_tx(&bars[stage], m.steer ? 2 * row_bytes : row_bytes);
+            bulk_g2s(dst, hbase + (size_t)v * H, row_bytes, &bars[stage]);
+            if (m.steer) bulk_g2s(dst + row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
+        }
+    };
+
+    RowMeta cur{};
+    if (vec < p.nvec) {
+        cur = load_meta<T>(p, vec);
+        issue(0, vec, cur);
+    }
+    cp_async_wait_all();
+    __syncthreads();  // weight row staged
+
+    for (int it = 0; vec < p.nvec; ++it) {
+        const int nxt = vec + stride;
+        RowMeta nm{};
+        if (nxt < p.nvec) {
+            nm = load_meta<T>(p, nxt);
+            issue((it + 1) & 1, nxt, nm);
+        }
+        const int stage = it & 1;
+        mbar_wait(&bars[stage], (unsigned)(it >> 1) & 1u);
+        T *h_s = reinterpret_cast<T *>(my_stage + (size_t)stage * 2 * row_bytes);
+        const T *v_s = reinterpret_cast<const T *>(my_stage + (size_t)stage * 2 * row_bytes + row_bytes);
+        T *hp = hbase + (size_t)vec * H;
+        T *yp = ybase + (size_t)vec * H;
+
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        if (cur.steer) {
+            const Injector<T, T> inj(cur.alpha);
+#pragma unroll 4
+            for (int g = lane; g < G; g += 32) {
+                Pack4<T> x = ld4<T>(h_s + 4 * g);
+                inj.apply(x, ld4<T>(v_s + 4 * g));
+                st4<T>(hp + 4 * g, x);   // h' to HBM
+                st4<T>(h_s + 4 * g, x);  // and kept for the second pass
+                sumsq4<T>(x, a0, a1, a2, a3);
+            }
+        } else {
+#pragma unroll 4
+            for (int g = lane; g < G; g += 32) sumsq4<T>(ld4<T>(h_s + 4 * g), a0, a1, a2, a3);
+        }
+        const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
+#pragma unroll 4
+        for (int g = lane; g < G; g += 32) {
+            Pack4<T> out;
+            norm4<T, VARIANT>(ld4<T>(h_s + 4 * g), r, ld4<T>(w_s + 4 * g), out);
+            st4<T>(yp + 4 * g, out);
+        }
+        fence_proxy_async();  // this lane's shared-memory accesses are ordered before later bulk copies
+        __syncwarp();         // every lane is done with this stage before it is refilled two iterations on
+        vec = nxt;
+        cur = nm;
+    }
+}
+
+template <typename T, int VARIANT, bool IEEE> static int launch_tma(const K2Params &p, cudaStream_t s) {
+    const size_t row_bytes = (size_t)p.H * sizeof(T);
+    const size_t budget = 220 * 1024;
+    if (row_bytes + 1024 + 4 * row_bytes > budget) return IA_ERR_TOO_LARGE;
+    int nwarps = (int)((budget - row_bytes - 1024) / (4 * row_bytes));
+    if (nwarps > 16) nwarps = 16;
+    const int sms = sm_count();
+    // small problems: do not start more warps than there are vectors per SM
+    const int per_sm = (p.nvec + sms - 1) / sms;
+    if (nwarps > per_sm) nwarps = per_sm < 1 ? 1 : per_sm;
+    const size_t bars_off = (row_bytes + 127) & ~(size_t)127;
+    const size_t smem = bars_off + (((size_t)nwarps * 2 * 8 + 127) & ~(size_t)127) + (size_t)nwarps * 4 * row_bytes;
+    auto kern = k2_tma_kernel<T, VARIANT, IEEE>;
+    // opt in to large dynamic shared memory once per instantiation and device (first call = a warm-up
+    // call, i.e. not under stream capture)
+    static bool configured[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!configured[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        configured[dev] = true;
+    }
+    long ctas = ((long)p.nvec + nwarps - 1) / nwarps;
+    if (ctas > sms) ctas = sms;
+    kern<<<(unsigned)ctas, 32 * nwarps, smem, s>>>(p);
+    return (int)cudaGetLastError();
+}
+
+template <typename T> static int tma_flags(const K2Params &p, int variant, int flags, cudaStream_t s) {
+    const bool ieee = (flags & IA_RSQRT_IEEE) != 0;
+    if (variant == IA_NORM_GEMMA) return ieee ? launch_tma<T, IA_NORM_GEMMA, true>(p, s) : launch_tma<T, IA_NORM_GEMMA, false>(p, s);
+    return ieee ? launch_tma<T, IA_NORM_LLAMA, true>(p, s) : launch_tma<T, IA_NORM_LLAMA, false>(p, s);
+}
+
+int launch_k2_tma(const K2Params &p, int dtype, int vec_dtype, int variant, int flags, cudaStream_t s) {
+    if (vec_dtype != dtype) return IA_ERR_DTYPE;         // table rows are bulk-copied as model-dtype rows
+    if ((p.H & 127) != 0) return IA_ERR_SHAPE;           // every lane owns the same number of groups
+    if (((size_t)p.H * (dtype == IA_F32 ? 4 : 2)) % 16 != 0) return IA_ERR_SHAPE;  // bulk copies move multiples of 16 bytes
+    switch (dtype) {
+    case IA_BF16: return tma_flags<__nv_bfloat16>(p, variant, flags, s);
+    case IA_F16: return tma_flags<__half>(p, variant, flags, s);
+    case IA_F32: return tma_flags<float>(p, variant, flags, s);
+    default: return IA_ERR_DTYPE;
+    }
+}
+
+}  // namespace ia

@@ -10,7 +10,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import (IA_BF16, IA_F16, IA_F32, IA_IMPL_TMA, IA_MODE_BASELINE, IA_MODE_POSNEG, IA_MODE_RAW,
+from ._lib import (IA_BF16, IA_F16, IA_F32, IA_IMPL_REGS, IA_IMPL_TMA, IA_MODE_BASELINE, IA_MODE_POSNEG, IA_MODE_RAW,
                    IA_MODE_SIMPLE, IA_NORM_GEMMA, IA_NORM_LLAMA, IA_RSQRT_IEEE, IA_STEER_ALL, check)
 
 _DTYPES = {torch.bfloat16: IA_BF16, torch.float16: IA_F16, torch.float32: IA_F32}
@@ -46,14 +46,15 @@ def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: s
                    vtable: Optional[torch.Tensor] = None, row_vec: Optional[torch.Tensor] = None,
                    row_alpha: Optional[torch.Tensor] = None, row_t0: Optional[torch.Tensor] = None,
                    pos0: int = 0, steer_all: bool = False, out: Optional[torch.Tensor] = None,
-                   ieee_rsqrt: bool = False, impl: str = "regs") -> torch.Tensor:
+                   ieee_rsqrt: bool = False, impl: str = "auto") -> torch.Tensor:
     """K2.  `h` [rows, T, H] is updated in place with the per-row injection; returns y = RMSNorm(h').
-    With row_vec None this is a plain RMSNorm of `variant`."""
+    With row_vec None this is a plain RMSNorm of `variant`.  impl: "auto" | "regs" | "tma"."""
     if h.dim() != 3:
         raise ValueError("h must be [rows, T, H]")
     rows, t_len, hid = h.shape
     y = torch.empty_like(h) if out is None else out
-    flags = (IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0) | (IA_IMPL_TMA if impl == "tma" else 0)
+    flags = ((IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
+             | {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS}[impl])
     lib = _lib.load()
     rc = lib.ia_inject_rmsnorm(
         _cuda(h, "h"), _cuda(y, "out", h.dtype), _cuda(vtable, "vtable"), _cuda(row_vec, "row_vec", torch.int32),

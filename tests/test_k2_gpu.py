@@ -49,7 +49,7 @@ def make_inputs(rows, T, H, dt, seed, n_vec=7, gemma=False):
 
 
 def run_kernel(h, vt, w, row_vec, alpha, t0, pos0, steer_all, eps, variant, dt, dev, vec_f32=False, ieee=True,
-               impl="regs"):
+               impl="auto"):
     from introspective_awareness_b200 import kernels
 
     h_t = to_model(h, dt, dev)
@@ -79,9 +79,50 @@ def test_bit_exact_against_oracle(dt, variant):
         for steer_all, pos0 in ((False, 0), (True, 7)):
             eps = 1e-5 if variant == "llama" else 1e-6
             want_h, want_y = K.inject_rmsnorm(h, vt_m, row_vec, alpha, t0, pos0, steer_all, w, eps, variant, dt)
-            got_h, got_y = run_kernel(h, vt_m, w, row_vec, alpha, t0, pos0, steer_all, eps, variant, dt, dev)
+            for impl in ("regs", "auto"):
+                got_h, got_y = run_kernel(h, vt_m, w, row_vec, alpha, t0, pos0, steer_all, eps, variant, dt, dev, impl=impl)
+                assert np.array_equal(got_h, want_h), (dt, variant, rows, T, H, steer_all, impl)
+                assert np.array_equal(got_y, want_y), (dt, variant, rows, T, H, steer_all, impl)
+
+
+@pytest.mark.parametrize("dt", ["bf16", "f16", "f32"])
+@pytest.mark.parametrize("variant", ["llama", "gemma"])
+def test_tma_staged_variant_bit_exact_against_oracle(dt, variant):
+    """IA_IMPL_TMA: per-warp cp.async.bulk + mbarrier ring.  Same bits as the oracle, including long
+    grid-stride runs (many ring wrap-arounds per warp) and mixed steered / control / late-t0 rows."""
+    dev = _dev()
+    shapes = [(5, 3, 128), (4, 9, 896), (7, 5, 1024), (4, 3, 3584), (9, 2, 4096), (3, 3, 5120), (700, 3, 256), (1, 1, 128)]
+    for k, (rows, T, H) in enumerate(shapes):
+        if dt == "f32" and H > 4096:
+            continue
+        h, vt, vt_m, w, row_vec, alpha, t0 = make_inputs(rows, T, H, dt, 500 + k, gemma=variant == "gemma")
+        for steer_all, pos0 in ((False, 0), (True, 3)):
+            eps = 1e-5 if variant == "llama" else 1e-6
+            want_h, want_y = K.inject_rmsnorm(h, vt_m, row_vec, alpha, t0, pos0, steer_all, w, eps, variant, dt)
+            got_h, got_y = run_kernel(h, vt_m, w, row_vec, alpha, t0, pos0, steer_all, eps, variant, dt, dev, impl="tma")
             assert np.array_equal(got_h, want_h), (dt, variant, rows, T, H, steer_all)
             assert np.array_equal(got_y, want_y), (dt, variant, rows, T, H, steer_all)
+
+
+def test_tma_variant_equals_register_kernel_at_full_size():
+    from introspective_awareness_b200 import kernels
+
+    dev = _dev()
+    rows, T, H = 200, 128, 4096
+    g = torch.Generator(device=dev).manual_seed(1)
+    h = torch.randn(rows, T, H, device=dev, generator=g).to(torch.bfloat16)
+    vt = (torch.randn(50, H, device=dev, generator=g) * 0.1).to(torch.bfloat16)
+    w = (1 + 0.02 * torch.randn(H, device=dev, generator=g)).to(torch.bfloat16)
+    row_vec = (torch.arange(rows, device=dev) % 51 - 1).to(torch.int32)
+    alpha = torch.tensor([1.0, 2.0, 4.0, 8.0], device=dev)[torch.arange(rows, device=dev) % 4].contiguous()
+    t0 = (100 - torch.arange(rows, device=dev) % 16).to(torch.int32)
+    outs = {}
+    for impl in ("regs", "tma"):
+        hh = h.clone()
+        y = kernels.inject_rmsnorm(hh, w, 1e-5, "llama", vtable=vt, row_vec=row_vec, row_alpha=alpha, row_t0=t0, impl=impl)
+        torch.cuda.synchronize()
+        outs[impl] = (hh, y)
+    assert torch.equal(outs["regs"][0], outs["tma"][0]) and torch.equal(outs["regs"][1], outs["tma"][1])
 
 
 def test_fp32_vector_table_with_bf16_model():

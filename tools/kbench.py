@@ -61,7 +61,7 @@ def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16):
     e = h.element_size()
 
     lib = _lib.load()
-    flags = _lib.IA_STEER_ALL | (_lib.IA_IMPL_TMA if impl == "tma" else 0)
+    flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS}[impl]
     args = (h.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(), t0.data_ptr(),
             w.data_ptr(), 1e-5, rows, T, H, 0, kernels._dt(h), kernels._dt(vt), kernels.VARIANTS[variant], flags,
             torch.cuda.current_stream().cuda_stream)
@@ -105,7 +105,7 @@ def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
-    ap.add_argument("--impl", default="regs")
+    ap.add_argument("--impl", default="auto", choices=["auto", "regs", "tma"])
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only-rows", type=int, default=0, help="run a single cold K2 shape (for ncu --set full)")
     args = ap.parse_args()
