@@ -200,6 +200,17 @@ IA_API int ia_meandiff_finalize(const void *concept_acts, int64_t n_concept, con
                          int32_t normalize, float *out_f32, void *out_rounded, float *out_norm,
                          void *workspace, int64_t workspace_bytes, int32_t dtype, void *stream);
 
+/*
+ * Runtime support (not a hot-path row of SURVEY.md §8): rotary position embedding of q and k in one
+ * launch, with the rounding points of transformers' apply_rotary_pos_emb
+ * (modeling_llama.py; reached through reference model_utils.py:338 and :847 like every other model op):
+ *     out = round(round(x*cos) + round(rotate_half(x)*sin)).
+ * q/q_out are [tokens, n_heads, head_dim], k/k_out [tokens, n_kv_heads, head_dim], cos/sin
+ * [tokens, head_dim], all contiguous in `dtype`; head_dim % 16 == 0.  Bit-identical to the eager ops.
+ */
+IA_API int ia_rope(const void *q, const void *k, const void *cosv, const void *sinv, void *q_out, void *k_out,
+            int64_t tokens, int64_t n_heads, int64_t n_kv_heads, int64_t head_dim, int32_t dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -41,6 +41,8 @@ _SIGNATURES = {
     "ia_gather_meandiff_static": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                           c_void_p, c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p, c_void_p,
                                           c_void_p, c_int32, c_void_p]),
+    "ia_rope": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
+                        c_int32, c_void_p]),
 }
 IA_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024
 

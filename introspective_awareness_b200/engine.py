@@ -119,6 +119,10 @@ class DecoderEngine:
         self.counters = {"k2_launches": 0, "k1_launches": 0}
         self.fused_norms = (self.device.type == "cuda") if fused_norms is None else fused_norms
         self.graph_extraction = True
+        # rotary embedding: one fused launch (same rounding points) instead of HF's ~8 eager kernels
+        import sys as _sys
+        self._rope_module = _sys.modules[type(first.self_attn).__module__]
+        self.fused_rope = self.device.type == "cuda"
         self._extract_graphs: Dict[tuple, tuple] = {}
         self.attention = attention
         if attention == "gqa":
@@ -172,14 +176,22 @@ class DecoderEngine:
         """`_run_layers` with this engine's attention function selected for the duration of the
         call only, so the HF model object keeps its stock behaviour for anyone else (the parity
         tests run the reference hook path on the very same model)."""
-        if self.attention != "gqa":
-            return self._run_layers(*args, **kwargs)
-        stock = self.cfg._attn_implementation
-        self.cfg._attn_implementation = ATTN_GQA
+        stock_attn = self.cfg._attn_implementation
+        stock_rope = getattr(self._rope_module, "apply_rotary_pos_emb", None)
+        if self.attention == "gqa":
+            self.cfg._attn_implementation = ATTN_GQA
+        if self.fused_rope and stock_rope is not None:
+            def fused(q, k, cos, sin, unsqueeze_dim=1):
+                out = kernels.rope(q, k, cos, sin) if unsqueeze_dim == 1 else None
+                return out if out is not None else stock_rope(q, k, cos, sin, unsqueeze_dim)
+
+            self._rope_module.apply_rotary_pos_emb = fused
         try:
             return self._run_layers(*args, **kwargs)
         finally:
-            self.cfg._attn_implementation = stock
+            self.cfg._attn_implementation = stock_attn
+            if stock_rope is not None:
+                self._rope_module.apply_rotary_pos_emb = stock_rope
 
     def _run_layers(self, h: torch.Tensor, pos_emb, masks, cache, steer: Optional[SteerSpec] = None,
                     pos0: int = 0, decode: bool = False, stop_after: Optional[int] = None,

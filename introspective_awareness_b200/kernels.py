@@ -189,3 +189,28 @@ def meandiff_finalize(concept_acts: torch.Tensor, base_sum: Optional[torch.Tenso
         out_n.data_ptr(), ws.data_ptr(), ws.numel(), _dt(concept_acts), _stream())
     check(rc, "ia_meandiff_finalize")
     return out_f32, out_r, out_n
+
+
+def rope(q: torch.Tensor, k: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor):
+    """Fused rotary embedding.  q [B, n_heads, T, D] and k [B, n_kv, T, D] must be transposed views of
+    contiguous [B, T, heads, D] tensors (what the HF projections produce); cos/sin [B, T, D] contiguous.
+    Returns (q_out, k_out) with the same shapes and strides.  Returns None when the layout is different
+    (the caller then uses the stock function)."""
+    if not (q.is_cuda and q.dim() == 4 and k.dim() == 4 and q.dtype in _DTYPES and k.dtype == q.dtype
+            and cos.dtype == q.dtype and sin.dtype == q.dtype):
+        return None
+    b, nh, t, d = q.shape
+    nkv = k.shape[1]
+    if d % 16 or k.shape != (b, nkv, t, d) or tuple(cos.shape) != (b, t, d) or tuple(sin.shape) != (b, t, d):
+        return None
+    if q.stride() != (t * nh * d, d, nh * d, 1) or k.stride() != (t * nkv * d, d, nkv * d, 1):
+        return None
+    if not (cos.is_contiguous() and sin.is_contiguous()):
+        return None
+    qo, ko = torch.empty_like(q), torch.empty_like(k)
+    if qo.stride() != q.stride() or ko.stride() != k.stride():
+        return None
+    rc = _lib.load().ia_rope(q.data_ptr(), k.data_ptr(), cos.data_ptr(), sin.data_ptr(), qo.data_ptr(), ko.data_ptr(),
+                             b * t, nh, nkv, d, _dt(q), _stream())
+    check(rc, "ia_rope")
+    return qo, ko
