@@ -103,49 +103,98 @@ struct K1Out {
     int ntiles;
 };
 
-// Concept rows c0, c0+cstep, ... of one (layer, tile): difference against the mean, both
-// roundings, norm partials.  RB row loads are issued before any store so that RB of them are in
-// flight (the compiler cannot hoist loads above the output stores on its own).
+// Eight consecutive elements as they sit in memory (kept packed while in flight).
+template <typename T> struct Raw8 { uint4 v; };
+template <> struct Raw8<float> { float4 a, b; };
+
+template <typename T> __device__ __forceinline__ Raw8<T> ldg_raw8(const T *p) {
+    Raw8<T> r;
+    r.v = __ldg(reinterpret_cast<const uint4 *>(p));
+    return r;
+}
+template <> __device__ __forceinline__ Raw8<float> ldg_raw8<float>(const float *p) {
+    Raw8<float> r;
+    r.a = __ldg(reinterpret_cast<const float4 *>(p));
+    r.b = __ldg(reinterpret_cast<const float4 *>(p) + 1);
+    return r;
+}
+template <typename T> __device__ __forceinline__ void widen8(const Raw8<T> &r, float (&f)[8]);
+template <> __device__ __forceinline__ void widen8<__nv_bfloat16>(const Raw8<__nv_bfloat16> &r, float (&f)[8]) {
+    f[0] = __uint_as_float(r.v.x << 16); f[1] = __uint_as_float(r.v.x & 0xffff0000u);
+    f[2] = __uint_as_float(r.v.y << 16); f[3] = __uint_as_float(r.v.y & 0xffff0000u);
+    f[4] = __uint_as_float(r.v.z << 16); f[5] = __uint_as_float(r.v.z & 0xffff0000u);
+    f[6] = __uint_as_float(r.v.w << 16); f[7] = __uint_as_float(r.v.w & 0xffff0000u);
+}
+template <> __device__ __forceinline__ void widen8<__half>(const Raw8<__half> &r, float (&f)[8]) {
+    const __half2 *h = reinterpret_cast<const __half2 *>(&r.v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { f[2 * i] = __low2float(h[i]); f[2 * i + 1] = __high2float(h[i]); }
+}
+template <> __device__ __forceinline__ void widen8<float>(const Raw8<float> &r, float (&f)[8]) {
+    f[0] = r.a.x; f[1] = r.a.y; f[2] = r.a.z; f[3] = r.a.w; f[4] = r.b.x; f[5] = r.b.y; f[6] = r.b.z; f[7] = r.b.w;
+}
+
+// Rows in flight per warp while emitting concept rows: 8 x 16 B for 16-bit dtypes (all of a warp's
+// share of 50 concepts in one round trip), 4 x 32 B for fp32.
+template <typename T> struct RowBatch { static constexpr int kRows = sizeof(T) == 4 ? 4 : 8; };
+
+// Issue the loads of concept rows cb, cb+cstep, ... (one batch).  Nothing here depends on the mean.
+template <typename T>
+__device__ __forceinline__ void load_batch(const RowSource<T> &csrc, int layer, int H, int col, bool active, int64_t cb,
+                                           int64_t cstep, Raw8<T> (&raw)[RowBatch<T>::kRows]) {
+#pragma unroll
+    for (int u = 0; u < RowBatch<T>::kRows; ++u) {
+        const int64_t c = cb + u * cstep;
+        if (active && c < csrc.n) raw[u] = ldg_raw8<T>(csrc.at(layer, c, H) + col);
+    }
+}
+
+// Difference against the mean, both roundings, stores and norm partials for one loaded batch.
+template <typename T>
+__device__ __forceinline__ void emit_batch(const RowSource<T> &csrc, int layer, int tile, int lane, int H, int col, bool active,
+                                           bool raw_mode, const float (&mean32)[8], const float (&meanr)[8], int64_t cb,
+                                           int64_t cstep, const Raw8<T> (&raw)[RowBatch<T>::kRows], const K1Out &o) {
+    const int64_t n_out = csrc.n;
+#pragma unroll
+    for (int u = 0; u < RowBatch<T>::kRows; ++u) {
+        const int64_t c = cb + u * cstep;
+        if (c >= n_out) break;  // warp-uniform
+        float a[8], v32[8], vr[8];
+        if (active) {
+            widen8<T>(raw[u], a);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            v32[i] = raw_mode ? a[i] : __fsub_rn(a[i], mean32[i]);
+            vr[i] = raw_mode ? a[i] : Elt<T>::rd(__fsub_rn(a[i], meanr[i]));
+        }
+        const int64_t orow = (int64_t)layer * n_out + c;
+        if (active) {
+            if (o.out_f32) store8<float>(o.out_f32 + orow * H + col, v32);
+            store8<T>(static_cast<T *>(o.out_rounded) + orow * H + col, vr);
+        }
+        const float p32 = sq8_warp(v32);
+        const float pr = sq8_warp(vr);
+        if (lane == 0) {
+            o.part32[orow * o.ntiles + tile] = p32;
+            o.partr[orow * o.ntiles + tile] = pr;
+        }
+    }
+}
+
+// Concept rows c0, c0+cstep, ... of one (layer, tile), a batch of loads in flight at a time (the
+// compiler cannot hoist loads above the output stores on its own).
 template <typename T>
 __device__ __forceinline__ void emit_rows(const RowSource<T> &csrc, int layer, int tile, int lane, int H, int col,
-                                          bool active, bool raw, const float (&mean32)[8], const float (&meanr)[8],
+                                          bool active, bool raw_mode, const float (&mean32)[8], const float (&meanr)[8],
                                           int64_t c0, int64_t cstep, const K1Out &o) {
-    constexpr int RB = 4;
-    const int64_t n_out = csrc.n;
-    for (int64_t cb = c0; cb < n_out; cb += cstep * RB) {
-        float a[RB][8];
-#pragma unroll
-        for (int u = 0; u < RB; ++u) {
-            const int64_t c = cb + u * cstep;
-            if (active && c < n_out) {
-                load8<T>(csrc.at(layer, c, H) + col, a[u]);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) a[u][i] = 0.f;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < RB; ++u) {
-            const int64_t c = cb + u * cstep;
-            if (c >= n_out) break;  // warp-uniform
-            float v32[8], vr[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                v32[i] = raw ? a[u][i] : __fsub_rn(a[u][i], mean32[i]);
-                vr[i] = raw ? a[u][i] : Elt<T>::rd(__fsub_rn(a[u][i], meanr[i]));
-            }
-            const int64_t orow = (int64_t)layer * n_out + c;
-            if (active) {
-                if (o.out_f32) store8<float>(o.out_f32 + orow * H + col, v32);
-                store8<T>(static_cast<T *>(o.out_rounded) + orow * H + col, vr);
-            }
-            const float p32 = sq8_warp(v32);
-            const float pr = sq8_warp(vr);
-            if (lane == 0) {
-                o.part32[orow * o.ntiles + tile] = p32;
-                o.partr[orow * o.ntiles + tile] = pr;
-            }
-        }
+    for (int64_t cb = c0; cb < csrc.n; cb += cstep * RowBatch<T>::kRows) {
+        Raw8<T> raw[RowBatch<T>::kRows];
+        load_batch<T>(csrc, layer, H, col, active, cb, cstep, raw);
+        emit_batch<T>(csrc, layer, tile, lane, H, col, active, raw_mode, mean32, meanr, cb, cstep, raw, o);
     }
 }
 
@@ -182,31 +231,46 @@ template <> __device__ __forceinline__ void lds8<float>(const unsigned char *p, 
 }
 
 // Sequential fp32 column sum of rows [r0, r1) for this CTA's tile.  All warps stage rows into
-// `stage` (cp.async, kStageBytes / row bytes rows per pass); warp 0 then adds them in row order.
+// shared memory with cp.async, in passes of `pass_rows` rows that alternate between the two halves
+// of `stage`; while warp 0 adds pass p in row order, the loads of pass p+1 are already in flight.
 // On return warp 0 holds the sums for columns col..col+7 in acc[]; other warps hold zeros.
 // With copy_to, the staged rows are also written out compactly (all warps, 16-byte stores).
 template <typename T>
 __device__ __forceinline__ void cta_column_sum(const RowSource<T> &src, int layer, int64_t r0, int64_t r1, int H, int col,
-                                               bool active, unsigned char *stage, float (&acc)[8], T *copy_to) {
+                                               bool active, unsigned char *stage, int pass_rows, float (&acc)[8], T *copy_to) {
     constexpr int kRowBytes = kTileCols * (int)sizeof(T);
-    constexpr int kPassRows = kStageBytes / kRowBytes;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-    for (int64_t p0 = r0; p0 < r1; p0 += kPassRows) {
-        const int n = (int)((r1 - p0) < kPassRows ? (r1 - p0) : kPassRows);
+    const int npass = (int)((r1 - r0 + pass_rows - 1) / pass_rows);
+    auto issue = [&](int p) {
+        const int64_t p0 = r0 + (int64_t)p * pass_rows;
+        const int n = (int)((r1 - p0) < pass_rows ? (r1 - p0) : pass_rows);
+        unsigned char *buf = stage + (size_t)(p & 1) * pass_rows * kRowBytes;
         if (active) {
             for (int r = warp; r < n; r += nwarps) {
                 const T *g = src.at(layer, p0 + r, H) + col;
-                unsigned char *d = stage + (size_t)r * kRowBytes + lane * 8 * sizeof(T);
+                unsigned char *d = buf + (size_t)r * kRowBytes + lane * 8 * sizeof(T);
                 cp_async16(d, g);
                 if (sizeof(T) == 4) cp_async16(d + 16, g + 4);
             }
         }
-        cp_async_drain();
+        asm volatile("cp.async.commit_group;\n" ::);
+    };
+    if (npass > 0) issue(0);
+    for (int p = 0; p < npass; ++p) {
+        if (p + 1 < npass) {
+            issue(p + 1);
+            asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        }
         __syncthreads();
+        const int64_t p0 = r0 + (int64_t)p * pass_rows;
+        const int n = (int)((r1 - p0) < pass_rows ? (r1 - p0) : pass_rows);
+        const unsigned char *buf = stage + (size_t)(p & 1) * pass_rows * kRowBytes;
         if (warp == 0 && active) {
-            const unsigned char *base = stage + lane * 8 * sizeof(T);
+            const unsigned char *base = buf + lane * 8 * sizeof(T);
             int r = 0;
             for (; r + 8 <= n; r += 8) {
                 float f[8][8];
@@ -227,20 +291,23 @@ __device__ __forceinline__ void cta_column_sum(const RowSource<T> &src, int laye
         }
         if (copy_to && active) {
             for (int r = warp; r < n; r += nwarps) {
-                const unsigned char *sp = stage + (size_t)r * kRowBytes + lane * 8 * sizeof(T);
+                const unsigned char *sp = buf + (size_t)r * kRowBytes + lane * 8 * sizeof(T);
                 unsigned char *dp = reinterpret_cast<unsigned char *>(copy_to + (p0 + r) * (int64_t)H + col);
                 *reinterpret_cast<uint4 *>(dp) = *reinterpret_cast<const uint4 *>(sp);
                 if (sizeof(T) == 4) *reinterpret_cast<uint4 *>(dp + 16) = *reinterpret_cast<const uint4 *>(sp + 16);
             }
         }
-        __syncthreads();  // the stage is overwritten by the next pass
+        __syncthreads();  // this half of the stage is refilled by pass p+2
     }
 }
 
-// Fused path: n_base <= 256 (or RAW).  One CTA (8 warps) per (layer, tile).
+// Fused path: n_base <= 256 (or RAW).  One CTA (4 warps; 4 CTAs per SM, so the 512 CTAs of a
+// 32-layer x 4096-column sweep are resident in a single wave) per (layer, tile).  Each warp's first batch
+// of concept rows is requested BEFORE the baseline rows are staged and summed: only the use of a
+// concept row depends on the mean, not its load, so both sets of loads share one memory round trip.
 template <typename T>
-__global__ void __launch_bounds__(256) k1_fused_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
-                                                       K1Out o) {
+__global__ void __launch_bounds__(128, 4) k1_fused_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
+                                                          int stage_rows, K1Out o) {
     extern __shared__ __align__(16) unsigned char smem[];
     float *mean_s = reinterpret_cast<float *>(smem);  // [2][kTileCols]: fp32 mean, rounded mean
     unsigned char *stage = smem + kMeanBytes;
@@ -249,12 +316,14 @@ __global__ void __launch_bounds__(256) k1_fused_kernel(RowSource<T> csrc, RowSou
     const int tile = blockIdx.x - layer * o.ntiles;
     const int col = tile * kTileCols + lane * 8;
     const bool active = col < H;
+    Raw8<T> first[RowBatch<T>::kRows];
+    load_batch<T>(csrc, layer, H, col, active, warp, nwarps, first);
     float mean32[8], meanr[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) { mean32[i] = 0.f; meanr[i] = 0.f; }
     if (!raw) {
         float acc[8];
-        cta_column_sum<T>(bsrc, layer, 0, bsrc.n, H, col, active, stage, acc, nullptr);
+        cta_column_sum<T>(bsrc, layer, 0, bsrc.n, H, col, active, stage, stage_rows, acc, nullptr);
         if (warp == 0) {
             const float nb = (float)bsrc.n;
 #pragma unroll
@@ -271,7 +340,9 @@ __global__ void __launch_bounds__(256) k1_fused_kernel(RowSource<T> csrc, RowSou
             meanr[i] = mean_s[kTileCols + lane * 8 + i];
         }
     }
-    emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, warp, nwarps, o);
+    emit_batch<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, warp, nwarps, first, o);
+    emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr,
+                 warp + (int64_t)nwarps * RowBatch<T>::kRows, nwarps, o);
 }
 
 // Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.
@@ -289,16 +360,25 @@ __global__ void __launch_bounds__(256) k1_segsum_kernel(RowSource<T> src, int n_
     const int64_t r0 = (int64_t)chunk * kChunkRows;
     const int64_t r1 = r0 + kChunkRows < src.n ? r0 + kChunkRows : src.n;
     float acc[8];
-    cta_column_sum<T>(src, layer, r0, r1, H, col, active, smem, acc, copy_to ? copy_to + (int64_t)layer * src.n * H : nullptr);
+    cta_column_sum<T>(src, layer, r0, r1, H, col, active, smem, kStageBytes / 2 / (kTileCols * (int)sizeof(T)), acc,
+                      copy_to ? copy_to + (int64_t)layer * src.n * H : nullptr);
     if (warp == 0 && active) store8<float>(part + ((int64_t)chunk * n_layers + layer) * H + col, acc);
 }
 
-// out[l, :] = part[0, l, :] + part[1, l, :] + ... in ascending chunk order.
+// out[l, :] = part[0, l, :] + part[1, l, :] + ... in ascending chunk order (loads 8 deep, adds in order).
 __global__ void k1_chunk_reduce_kernel(const float *part, float *out, int64_t per_chunk, int nchunks) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= per_chunk) return;
     float s = part[i];
-    for (int c = 1; c < nchunks; ++c) s = __fadd_rn(s, part[(int64_t)c * per_chunk + i]);
+    int c = 1;
+    for (; c + 8 <= nchunks; c += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldg(part + (int64_t)(c + u) * per_chunk + i);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) s = __fadd_rn(s, v[u]);
+    }
+    for (; c < nchunks; ++c) s = __fadd_rn(s, __ldg(part + (int64_t)c * per_chunk + i));
     out[i] = s;
 }
 
@@ -437,7 +517,7 @@ static int run_segsum(const RowSource<T> &src, int L, int H, float *part, float 
     if (e != cudaSuccess) return (int)e;
     if (nch > 1) {
         const int64_t per = (int64_t)L * H;
-        k1_chunk_reduce_kernel<<<(unsigned)((per + 255) / 256), 256, 0, s>>>(part, sum_out, per, nch);
+        k1_chunk_reduce_kernel<<<(unsigned)((per + 63) / 64), 64, 0, s>>>(part, sum_out, per, nch);
         e = cudaGetLastError();
     }
     return (int)e;
@@ -474,10 +554,15 @@ static int gather_meandiff_t(const void *const *cptrs, int64_t Tc, const int32_t
     K1Out o{out_f32, out_rounded, ws + wl.part32, ws + wl.partr, ntiles};
     const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : nc;
     if (mode != IA_MODE_POSNEG && (mode == IA_MODE_RAW || nb <= kChunkRows)) {
-        const int smem = kMeanBytes + (mode == IA_MODE_RAW ? 0 : kStageBytes);
+        // all baseline rows in one pass when they fit half the staging budget each way (two halves of
+        // `stage_rows` rows), otherwise two alternating half-size passes
+        const int row_bytes = kTileCols * (int)sizeof(T);
+        const int half_rows = kStageBytes / 2 / row_bytes;
+        const int stage_rows = nb <= 2 * half_rows ? (int)std::max<int64_t>(nb, 1) : half_rows;
+        const int smem = kMeanBytes + (mode == IA_MODE_RAW ? 0 : (nb <= 2 * half_rows ? stage_rows : 2 * stage_rows) * row_bytes);
         cudaError_t e = cudaFuncSetAttribute(k1_fused_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMeanBytes + kStageBytes);
         if (e != cudaSuccess) return (int)e;
-        k1_fused_kernel<T><<<(unsigned)(L * ntiles), 256, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, o);
+        k1_fused_kernel<T><<<(unsigned)(L * ntiles), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, o);
         e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         const int64_t rows = (int64_t)L * n_out;

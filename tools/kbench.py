@@ -108,6 +108,7 @@ def main():
     ap.add_argument("--impl", default="auto", choices=["auto", "regs", "tma"])
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only-rows", type=int, default=0, help="run a single cold K2 shape (for ncu --set full)")
+    ap.add_argument("--only-k1", action="store_true", help="run only the K1 ladder")
     args = ap.parse_args()
     peak, src = peak_gbs()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda:0")
@@ -118,6 +119,8 @@ def main():
         return
     rows_ladder = [200, 3000, 25600] if args.quick else [200, 3000, 25600, 262144]
     hs = [4096] if args.quick else [896, 3584, 4096, 5120]
+    if args.only_k1:
+        hs = []
     for H in hs:
         for rows in rows_ladder:
             if rows * H * 2 * 2 > 40e9:
