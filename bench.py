@@ -231,6 +231,7 @@ def run_ours(args):
         step_resident()
     sampler = ClockSampler(local) if rank == 0 else None
     eng.k2_events = []
+    launches_before = dict(eng.counters)
     if args.ncu_window:
         # profiler window = the last timed step only (ncu --profile-from-start off -c N)
         real_step, seen = step_resident, [0]
@@ -242,6 +243,7 @@ def run_ours(args):
             real_step()
 
     ms_res = timed(step_resident, args.steps)
+    launches_after = dict(eng.counters)
     if args.ncu_window:
         torch.cuda.profiler.stop()
         step_resident = real_step
@@ -267,8 +269,12 @@ def run_ours(args):
     h2d = sum(t.numel() * t.element_size() for t in (h_c_ids, h_c_mask, h_b_ids, h_b_mask, h_ids, h_mask)) \
         + N_CONCEPTS * H * 2 + rows * (4 + 4 + 4)
     d2h = N_CONCEPTS * H * 2 + rows * N_NEW * 8
-    k1_launches = 2 if world == 1 else 2 * 2 + 2  # fused+norm | 2x segsum(+reduce) + finalize+norm
-    launches = args.steps * (N_NEW + k1_launches)
+    # our kernels launched inside the value-timed region on this rank (counted by the engine: eager
+    # launches directly, graph replays by the launches recorded at capture)
+    launches_by_kernel = {k: launches_after[k] - launches_before[k] for k in launches_before}
+    if world > 1:
+        launches_by_kernel["k1_launches"] += args.steps * 4  # 2x gather_segsum + finalize + norm, called outside the engine
+    launches = sum(launches_by_kernel.values())
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:  # reported at N=1 only
@@ -289,7 +295,7 @@ def run_ours(args):
             },
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": launches,
+            "gpu_launches": launches, "gpu_launches_by_kernel": launches_by_kernel,
             "roofline": {"kernel": "ia_inject_rmsnorm (ia::k2_tma_kernel: fused inject+RMSNorm, cp.async.bulk staged), prompt-pass launch", "bound": "hbm",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
                          "traffic": traffic_from_profiles(), "peak_source": peak_src,

@@ -116,7 +116,9 @@ class DecoderEngine:
         self.head_dim = getattr(cfg, "head_dim", None) or cfg.hidden_size // cfg.num_attention_heads
         self.softcap = getattr(cfg, "final_logit_softcapping", None)
         self.sliding_window = getattr(cfg, "sliding_window", None) if self.is_gemma2 else None
-        self.counters = {"k2_launches": 0, "k1_launches": 0}
+        # launches of OUR kernels (K2 incl. plain-norm use, K1 calls, fused rope); graph replays add the
+        # number of launches recorded when the graph was captured
+        self.counters = {"k2_launches": 0, "k1_launches": 0, "rope_launches": 0}
         self.fused_norms = (self.device.type == "cuda") if fused_norms is None else fused_norms
         self.graph_extraction = True
         # rotary embedding: one fused launch (same rounding points) instead of HF's ~8 eager kernels
@@ -183,7 +185,10 @@ class DecoderEngine:
         if self.fused_rope and stock_rope is not None:
             def fused(q, k, cos, sin, unsqueeze_dim=1):
                 out = kernels.rope(q, k, cos, sin) if unsqueeze_dim == 1 else None
-                return out if out is not None else stock_rope(q, k, cos, sin, unsqueeze_dim)
+                if out is not None:
+                    self.counters["rope_launches"] += 1
+                    return out
+                return stock_rope(q, k, cos, sin, unsqueeze_dim)
 
             self._rope_module.apply_rotary_pos_emb = fused
         try:
@@ -316,14 +321,20 @@ class DecoderEngine:
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
+            before = dict(self.counters)
             with torch.cuda.graph(g):
                 outs = self._capture_layers_eager(ids_s, mask_s, layer_indices, padded)
+            g.ia_launches = {k: self.counters[k] - before[k] for k in before}
+            for k in before:
+                self.counters[k] = before[k]
             entry = (g, ids_s, mask_s, outs)
             self._extract_graphs[key] = entry
         g, ids_s, mask_s, outs = entry
         ids_s.copy_(input_ids, non_blocking=True)
         mask_s.copy_(attention_mask, non_blocking=True)
         g.replay()
+        for k, v in g.ia_launches.items():
+            self.counters[k] += v
         return outs
 
     @torch.inference_mode()
@@ -347,7 +358,7 @@ class DecoderEngine:
         out = kernels.gather_meandiff(
             cl, bl, mode, normalize, concept_tok=tok(cl[0].shape[1], cl[0].shape[0]),
             base_tok=None if bl is None else tok(bl[0].shape[1], bl[0].shape[0]), want_f32=want_f32)
-        self.counters["k1_launches"] += 1
+        self.counters["k1_launches"] += 2  # fused gather+mean-diff kernel + norm kernel
         return out
 
     # -- generation ---------------------------------------------------------------------------
@@ -432,8 +443,13 @@ class Session:
         graphs = []
         for s in range(1, self.N):
             g = torch.cuda.CUDAGraph()
+            before = dict(self.eng.counters)
             with torch.cuda.graph(g, pool=self.pool):
                 self._step(s, steer, greedy, eos, pad)
+            # launches recorded into this graph (they did not run): credited on every replay instead
+            g.ia_launches = {k: self.eng.counters[k] - before[k] for k in before}
+            for k in before:
+                self.eng.counters[k] = before[k]
             if self.pool is None:
                 self.pool = g.pool()
             graphs.append(g)
@@ -501,6 +517,8 @@ class Session:
             for s in range(1, self.N):
                 if graphs is not None:
                     graphs[s - 1].replay()
+                    for k, v in graphs[s - 1].ia_launches.items():
+                        eng.counters[k] += v
                 else:
                     self._step(s, st, greedy, eos_token_id, pad_token_id)
                 if keep_logits:

@@ -1,0 +1,117 @@
+"""Layer x strength sweep on the batched runtime, writing the reference's on-disk formats
+ so that the reference's `--reevaluate-judge`, plotting and transcript tools
+(detect_injected_thoughts.py:1400-1506, :560, :771, :1080) can consume the output unchanged:
+
+    <out>/<model>/layer_{fraction:.2f}_strength_{strength}/results.json   {"results", "metrics", "n_samples"}
+    <out>/<model>/layer_{fraction:.2f}_strength_{strength}/results.csv    one row per trial
+    <out>/<model>/vectors/layer_{fraction:.2f}/{concept}.pt               bare torch.save of the vector
+
+(reference detect_injected_thoughts.py:1651, :1780-1787, :2136-2157; eval_utils.py:894-919).
+
+What differs from the reference's sweep (detect_injected_thoughts.py:1551-1561, :1645-1647):
+all layer fractions are extracted from ONE pair of forwards (K1 over all layers), each layer's
+concept x strength x trial grid is ONE steered batch sequence with per-row strength (K2), control
+trials are generated once per layer instead of once per (layer, strength), and layers are dealt
+round-robin to the ranks of a `torch.distributed` job.  The LLM judge stays outside (host-side,
+untimed): metrics here are the reference's keyword metrics (`check_concept_mentioned`).
+"""
+
+from __future__ import annotations
+
+import csv
+import json
+from pathlib import Path
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import grid, parallel
+from . import vector_utils as vu
+from .model_utils import get_layer_at_fraction
+
+RESULT_FIELDS = ["concept", "trial", "response", "injected", "layer", "layer_fraction", "strength", "detected", "trial_type"]
+
+
+def config_dir(base: Path, layer_fraction: float, strength: float) -> Path:
+    return Path(base) / f"layer_{layer_fraction:.2f}_strength_{strength}"
+
+
+def keyword_metrics(results: Sequence[dict]) -> Dict[str, float]:
+    """Detection / identification rates from the `detected` keyword flag, named as the reference
+    names its per-config metrics (detect_injected_thoughts.py:2139-2150)."""
+    def rate(rows):
+        rows = list(rows)
+        return sum(bool(r["detected"]) for r in rows) / len(rows) if rows else 0.0
+
+    inj = [r for r in results if r["trial_type"] == "injection"]
+    ctl = [r for r in results if r["trial_type"] == "control"]
+    frc = [r for r in results if r["trial_type"] == "forced"]
+    hit, fa = rate(inj), rate(ctl)
+    n = len(inj) + len(ctl)
+    acc = (sum(bool(r["detected"]) for r in inj) + sum(not r["detected"] for r in ctl)) / n if n else 0.0
+    return {"detection_hit_rate": hit, "detection_false_alarm_rate": fa, "detection_accuracy": acc,
+            "forced_identification_accuracy": rate(frc)}
+
+
+def write_config(base: Path, layer_fraction: float, layer_idx: int, strength: float, results: List[dict],
+                 temperature: float, max_tokens: int, extra_metrics: Optional[dict] = None) -> Path:
+    """results.json + results.csv for one (layer fraction, strength) configuration."""
+    d = config_dir(base, layer_fraction, strength)
+    d.mkdir(parents=True, exist_ok=True)
+    metrics = dict(keyword_metrics(results), layer_fraction=layer_fraction, layer_idx=layer_idx, strength=strength,
+                   temperature=temperature, max_tokens=max_tokens)
+    metrics.update(extra_metrics or {})
+    with open(d / "results.json", "w") as f:
+        json.dump({"results": results, "metrics": metrics, "n_samples": len(results)}, f, indent=2)
+    with open(d / "results.csv", "w", newline="") as f:
+        w = csv.DictWriter(f, fieldnames=RESULT_FIELDS, extrasaction="ignore")
+        w.writeheader()
+        w.writerows(results)
+    return d
+
+
+def save_vectors(base: Path, layer_fraction: float, vectors: Dict[str, torch.Tensor]) -> None:
+    d = Path(base) / "vectors" / f"layer_{layer_fraction:.2f}"
+    d.mkdir(parents=True, exist_ok=True)
+    for concept, vec in vectors.items():
+        torch.save(vec, d / f"{concept}.pt")
+
+
+def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], layer_fractions: Sequence[float],
+              strengths: Sequence[float], n_trials: int = 30, max_new_tokens: int = 100, temperature: float = 1.0,
+              batch_size: int = 256, output_dir: Optional[str] = None, extraction_method: str = "baseline",
+              with_forced: bool = True, save_vector_files: bool = True) -> Dict[tuple, List[dict]]:
+    """Runs the whole grid; returns {(layer_fraction, strength): results} for the layers this rank owns
+    and (if output_dir) writes the reference's files for them.  Trial split as the reference:
+    n_injection = n_trials // 2, n_control = n_trials - n_injection, forced = n_injection
+    (detect_injected_thoughts.py:1792-1799)."""
+    rank, world = parallel.world()
+    concepts = list(concepts)
+    fractions = list(layer_fractions)
+    layer_of = {f: get_layer_at_fraction(model, f) for f in fractions}
+    uniq_layers = sorted(set(layer_of.values()))
+    by_layer = vu.extract_concept_vectors_multi_layer(model, concepts, list(baseline_words), uniq_layers,
+                                                      extraction_method=extraction_method)
+    base = None
+    if output_dir is not None:
+        base = Path(output_dir) / str(model.model_name).replace("/", "_")
+        if save_vector_files and rank == 0:
+            for f in fractions:
+                save_vectors(base, f, by_layer[layer_of[f]])
+    n_inj = n_trials // 2
+    n_ctl = n_trials - n_inj
+    out: Dict[tuple, List[dict]] = {}
+    for f in parallel.shard_round_robin(fractions, rank, world):
+        layer = layer_of[f]
+        rows = grid.layer_trials(concepts, strengths, n_inj, n_ctl, n_inj if with_forced else 0, dedupe_control=True)
+        results = grid.run_layer(model, layer, by_layer[layer], rows, max_new_tokens, temperature, batch_size,
+                                 layer_fraction=f)
+        control = [r for r in results if r["trial_type"] == "control"]
+        for a in strengths:
+            # the reference stores the (strength-independent) control trials in every strength's file
+            cfg = [r for r in results if r["trial_type"] != "control" and r["strength"] == float(a)]
+            cfg += [dict(r, strength=float(a)) for r in control]
+            out[(f, float(a))] = cfg
+            if base is not None:
+                write_config(base, f, layer, float(a), cfg, temperature, max_new_tokens)
+    return out

@@ -200,3 +200,36 @@ def test_string_api_matches_hook_path_text():
     b = w.steered_generate_ids(ids, mask, 1, torch.stack([vecs[c] for c in concepts]), [0, 1, 2], [4.0] * 3, t0, 8,
                                temperature=1.0, generator=g2).clone()
     assert torch.equal(a, b)
+
+
+def test_sweep_driver_end_to_end(tmp_path):
+    """Multi-layer extraction + one batch per layer with per-row strength + reference file layout."""
+    import json
+
+    from introspective_awareness_b200 import sweep, vector_utils as vu
+
+    w = _wrapper("tiny-llama", torch.bfloat16, 7)
+    w.model_name = "tiny/llama"
+    concepts = ["Dust", "Trees", "Oceans"]
+    out = sweep.run_sweep(w, concepts, vu.get_baseline_words(10), [0.3, 0.8], [2.0, 8.0], n_trials=4, max_new_tokens=6,
+                          temperature=0.0, batch_size=16, output_dir=str(tmp_path))
+    assert set(out) == {(0.3, 2.0), (0.3, 8.0), (0.8, 2.0), (0.8, 8.0)}
+    base = tmp_path / "tiny_llama"
+    blob = json.load(open(base / "layer_0.80_strength_8.0" / "results.json"))
+    assert blob["n_samples"] == 3 * (2 + 2 + 2) and blob["metrics"]["layer_idx"] == 3
+    kinds = {r["trial_type"] for r in blob["results"]}
+    assert kinds == {"injection", "control", "forced"}
+    assert all(r["strength"] == 8.0 for r in blob["results"])
+    v = torch.load(base / "vectors" / "layer_0.30" / "Trees.pt")
+    assert v.shape == (w.engine.hidden,) and v.dtype == torch.bfloat16
+    # one batch per layer must equal the reference-style call for a single (layer, strength) config
+    vecs = vu.extract_concept_vectors_batch(w, concepts, vu.get_baseline_words(10), layer_idx=3)
+    assert torch.equal(vecs["Trees"], torch.load(base / "vectors" / "layer_0.80" / "Trees.pt"))
+    from introspective_awareness_b200 import steering_utils as su
+
+    inj = [r for r in blob["results"] if r["trial_type"] == "injection"]
+    built = [su.build_trial(w, r["trial"]) for r in inj]
+    texts = w.generate_batch_with_multi_steering([p for p, _ in built], 3, [vecs[r["concept"]] for r in inj], strength=8.0,
+                                                 max_new_tokens=6, temperature=0.0,
+                                                 steering_start_positions=[t for _, t in built])
+    assert texts == [r["response"] for r in inj]

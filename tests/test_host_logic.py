@@ -173,3 +173,34 @@ def test_grid_rows_and_dedupe():
     assert len(dedup) == 4 * 50 * 30 + 50 * 15
     assert [len(c) for c in grid.chunk(rows, 64)] == [64, 64, 64, 8]
     assert rows[0] == grid.Trial("c0", 1.0, 1, "injection")
+
+
+def test_sweep_writers_use_the_reference_wire_format(tmp_path):
+    """results.json / results.csv / vectors layout the reference's re-judge, plotting and transcript
+    tools read (detect_injected_thoughts.py:1651, :1780-1787, :2136-2157; eval_utils.py:910-914)."""
+    import csv
+    import json
+
+    from introspective_awareness_b200 import sweep
+
+    rows = [
+        {"concept": "Dust", "trial": 1, "response": "I notice dust", "injected": True, "layer": 22, "layer_fraction": 0.7,
+         "strength": 4.0, "detected": True, "trial_type": "injection"},
+        {"concept": "Dust", "trial": 1, "response": "nothing", "injected": False, "layer": 22, "layer_fraction": 0.7,
+         "strength": 4.0, "detected": False, "trial_type": "control"},
+        {"concept": "Dust", "trial": 1, "response": "about trees", "injected": True, "layer": 22, "layer_fraction": 0.7,
+         "strength": 4.0, "detected": False, "trial_type": "forced"},
+    ]
+    d = sweep.write_config(tmp_path / "llama_8b", 0.7, 22, 4.0, rows, temperature=1.0, max_tokens=100)
+    assert d.name == "layer_0.70_strength_4.0"
+    blob = json.load(open(d / "results.json"))
+    assert set(blob) == {"results", "metrics", "n_samples"} and blob["n_samples"] == 3
+    assert blob["results"][0] == rows[0]
+    m = blob["metrics"]
+    assert m["detection_hit_rate"] == 1.0 and m["detection_false_alarm_rate"] == 0.0 and m["detection_accuracy"] == 1.0
+    assert m["forced_identification_accuracy"] == 0.0 and m["layer_idx"] == 22 and m["strength"] == 4.0
+    got = list(csv.DictReader(open(d / "results.csv")))
+    assert len(got) == 3 and got[0]["concept"] == "Dust" and got[1]["trial_type"] == "control"
+    sweep.save_vectors(tmp_path / "llama_8b", 0.7, {"Dust": torch.arange(4.0)})
+    v = torch.load(tmp_path / "llama_8b" / "vectors" / "layer_0.70" / "Dust.pt")
+    assert torch.equal(v, torch.arange(4.0))
