@@ -532,12 +532,17 @@ class Session:
         return self.out_ids
 
     @staticmethod
-    def _sample(logits: torch.Tensor, temperature: float, top_k: Optional[int], generator) -> torch.Tensor:
-        """HF `do_sample=True` defaults: temperature, then top-k 50, then multinomial
-        (reference model_utils.py:833-837 passes only temperature)."""
+    def sampling_probs(logits: torch.Tensor, temperature: float, top_k: Optional[int]) -> torch.Tensor:
+        """The distribution HF `generate(do_sample=True, temperature=...)` samples from with its default
+        generation config: temperature scaling, then top-k 50 (TemperatureLogitsWarper,
+        TopKLogitsWarper), then softmax.  reference model_utils.py:833-837 passes only temperature."""
         lg = logits.float() / temperature
         if top_k is not None and 0 < top_k < lg.shape[-1]:
             kth = lg.topk(top_k, dim=-1).values[..., -1:]
             lg = lg.masked_fill(lg < kth, float("-inf"))
-        probs = torch.softmax(lg, dim=-1)
+        return torch.softmax(lg, dim=-1)
+
+    @staticmethod
+    def _sample(logits: torch.Tensor, temperature: float, top_k: Optional[int], generator) -> torch.Tensor:
+        probs = Session.sampling_probs(logits, temperature, top_k)
         return torch.multinomial(probs, 1, generator=generator).squeeze(-1)

@@ -77,6 +77,22 @@ ARCHS: Dict[str, dict] = {
         rope_scaling=dict(rope_type="llama3", factor=8.0, low_freq_factor=1.0,
                           high_freq_factor=4.0, original_max_position_embeddings=8192),
     ),
+    # Real Gemma-2-9B and Qwen2.5-32B widths / head layouts / vocabularies with few layers, for the
+    # same-device parity tests of BASELINE configs[3] and [4] (Gemma: 4 norms per layer, 1 + w scaling,
+    # soft-capping, sliding window; Qwen: H = 5120, q/k/v biases).
+    "gemma-2-9b-4layer": dict(
+        family="gemma2", vocab_size=256000, hidden_size=3584, intermediate_size=14336,
+        num_hidden_layers=4, num_attention_heads=16, num_key_value_heads=8, head_dim=256,
+        rms_norm_eps=1e-6, rope_theta=10000.0, max_position_embeddings=8192,
+        sliding_window=4096, query_pre_attn_scalar=256,
+        attn_logit_softcapping=50.0, final_logit_softcapping=30.0,
+    ),
+    "qwen2.5-32b-2layer": dict(
+        family="qwen2", vocab_size=152064, hidden_size=5120, intermediate_size=27648,
+        num_hidden_layers=2, num_attention_heads=40, num_key_value_heads=8,
+        rms_norm_eps=1e-6, rope_theta=1000000.0, max_position_embeddings=32768,
+        tie_word_embeddings=False,
+    ),
 }
 
 

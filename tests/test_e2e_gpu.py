@@ -101,6 +101,8 @@ def test_config1_qwen05b_fp32_matches_real_reference():
 def _hook_path_vs_ours(arch, layer, rows, t_max, t_min, n_new, alphas, seed, n_concepts=50, attention="hf", **overrides):
     from introspective_awareness_b200.synthetic import synthetic_prompt_ids
 
+    if seed is None:
+        torch.manual_seed(1234)
     w = _wrapper(arch, torch.bfloat16, seed, attention=attention, **overrides)
     V = w.model.config.vocab_size
     ids, mask, lens = synthetic_prompt_ids(rows, t_max, t_min, V, seed=1)
@@ -140,6 +142,21 @@ def test_same_device_hook_path_llama_8b_dims():
     diff = (ol - rl).abs().max().item()
     same_rows = (ours == ref).all(dim=1).float().mean().item()
     print(f"max |logit diff| = {diff:.4g}; rows with identical 32-token greedy paths: {same_rows:.3f}")
+    assert diff <= 2e-2
+    assert torch.equal(ours, ref)
+
+
+@pytest.mark.parametrize("arch,layer", [("gemma-2-9b-4layer", 1), ("gemma-2-9b-4layer", 3), ("qwen2.5-32b-2layer", 0)])
+def test_same_device_hook_path_gemma2_9b_and_qwen_32b_dims(arch, layer):
+    """BASELINE configs[3]/[4] shapes: Gemma-2 (post+pre norm fusion variant, incl. injection at the
+    LAST layer, fused with model.norm) and Qwen2.5-32B (H = 5120) against the hook path on the same GPU,
+    in bench.py's runtime mode."""
+    # seed=None: Hugging Face's own initialisation, on the GPU (both paths share the model object)
+    ours, ol, ref, rl = _hook_path_vs_ours(arch, layer, rows=96, t_max=64, t_min=48, n_new=32,
+                                           alphas=[1.0, 2.0, 4.0, 8.0], seed=None, n_concepts=24, attention="gqa")
+    diff = (ol - rl).abs().max().item()
+    same_rows = (ours == ref).all(dim=1).float().mean().item()
+    print(f"{arch} L={layer}: max |logit diff| = {diff:.4g}; identical 32-token rows: {same_rows:.3f}")
     assert diff <= 2e-2
     assert torch.equal(ours, ref)
 

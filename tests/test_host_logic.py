@@ -204,3 +204,21 @@ def test_sweep_writers_use_the_reference_wire_format(tmp_path):
     sweep.save_vectors(tmp_path / "llama_8b", 0.7, {"Dust": torch.arange(4.0)})
     v = torch.load(tmp_path / "llama_8b" / "vectors" / "layer_0.70" / "Dust.pt")
     assert torch.equal(v, torch.arange(4.0))
+
+
+def test_sampling_distribution_matches_hf_warpers():
+    """temperature > 0 (the reference's default, detect_injected_thoughts.py:72): our sampler draws from
+    exactly the distribution HF's default sampling pipeline builds (temperature, then top-k 50)."""
+    from transformers.generation.logits_process import TemperatureLogitsWarper, TopKLogitsWarper
+
+    from introspective_awareness_b200.engine import Session
+
+    g = torch.Generator().manual_seed(0)
+    logits = torch.randn(5, 300, generator=g) * 3
+    for temp, k in ((1.0, 50), (0.7, 50), (1.3, None)):
+        scores = TemperatureLogitsWarper(temp)(None, logits.clone())
+        if k is not None:
+            scores = TopKLogitsWarper(top_k=k)(None, scores)
+        want = torch.softmax(scores, dim=-1)
+        got = Session.sampling_probs(logits, temp, k)
+        assert torch.allclose(got, want, atol=1e-7) and ((got > 0) == (want > 0)).all()
