@@ -38,12 +38,6 @@ __device__ __forceinline__ float warp_total(float a0, float a1, float a2, float 
     return __shfl_sync(FULL, s, 0);
 }
 
-template <typename T, int VARIANT> __device__ __forceinline__ float norm_out(float x, float r, float w) {
-    float n = __fmul_rn(x, r);
-    if (VARIANT == IA_NORM_LLAMA) return Elt<T>::rd(__fmul_rn(w, Elt<T>::rd(n)));
-    return Elt<T>::rd(__fmul_rn(n, __fadd_rn(1.0f, w)));
-}
-
 // cp.async (LDGSTS) of one 4-element group: asynchronous, no register staging.
 template <int BYTES> __device__ __forceinline__ void cp_async_group(void *smem_dst, const void *gsrc) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);

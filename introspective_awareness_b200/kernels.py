@@ -5,7 +5,7 @@ libia_b200.so.  Every function raises if the inputs are not CUDA tensors — the
 
 from __future__ import annotations
 
-from typing import List, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 
