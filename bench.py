@@ -167,15 +167,16 @@ def run_ours(args):
     blo, bhi = parallel.shard_contiguous(N_BASE, rank, world)
     sweep_idx = sweep.index(my_layer)
 
-    def extract_resident():
-        """-> [50, H] device vectors for this rank's layer."""
+    def extract_resident(ci=None, cm=None, bi=None, bm=None):
+        """-> [50, H] device vectors for this rank's layer (inputs default to the HBM-resident copies)."""
+        ci, cm, bi, bm = (c_ids, c_mask, b_ids, b_mask) if ci is None else (ci, cm, bi, bm)
         if world == 1:
-            _, vr, _ = eng.extract_vectors(c_ids, c_mask, b_ids, b_mask, [my_layer], want_f32=False)
+            _, vr, _ = eng.extract_vectors(ci, cm, bi, bm, [my_layer], want_f32=False)
             return vr[0]
         # prompt-sharded: this rank forwards its slice of both prompt sets, for every layer of this step
         uniq = sorted(set(sweep))
-        cl = eng.capture_layers(c_ids[clo:chi], c_mask[clo:chi], uniq, slot=0)
-        bl = eng.capture_layers(b_ids[blo:bhi], b_mask[blo:bhi], uniq, slot=1)
+        cl = eng.capture_layers(ci[clo:chi], cm[clo:chi], uniq, slot=0)
+        bl = eng.capture_layers(bi[blo:bhi], bm[blo:bhi], uniq, slot=1)
         crow, _ = kernels.gather_segsum(cl, want_rows=True)
         _, bsum = kernels.gather_segsum(bl, want_rows=False)
         parallel.allreduce_sum_(bsum)
@@ -197,11 +198,7 @@ def run_ours(args):
     def step_e2e():
         """Public API with host buffers: ids/masks from pinned host memory, vectors returned to the host
         (as the reference's extraction does), generation fed with host vectors, ids read back."""
-        if world == 1:
-            _, vr, _ = eng.extract_vectors(h_c_ids, h_c_mask, h_b_ids, h_b_mask, [my_layer], want_f32=False)
-            vec_host = vr[0].cpu()
-        else:
-            vec_host = extract_resident().cpu()
+        vec_host = extract_resident(h_c_ids, h_c_mask, h_b_ids, h_b_mask).cpu()
         out = w.steered_generate_ids(h_ids, h_mask, my_layer, vec_host, wl["row_vec"], wl["row_alpha"], wl["t0"], N_NEW,
                                      temperature=0.0)
         host_ids = out.cpu()
