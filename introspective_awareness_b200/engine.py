@@ -286,7 +286,9 @@ class DecoderEngine:
             if not 0 <= i < self.n_layers:
                 raise IndexError(f"layer {i} out of range")
         padded = not bool(attention_mask.all())
-        if self.device.type == "cuda" and self.graph_extraction:
+        # small (launch-bound) forwards replay as a CUDA graph; large ones are GPU-bound anyway and a
+        # graph would pin their activations in a private pool
+        if self.device.type == "cuda" and self.graph_extraction and input_ids.numel() <= 16384:
             return self._capture_layers_graphed(input_ids, attention_mask, layer_indices, padded, slot)
         return self._capture_layers_eager(input_ids.to(self.device), attention_mask.to(self.device), layer_indices, padded)
 

@@ -204,6 +204,8 @@ class ModelWrapper:
                                            steering_start_positions: Optional[List[int]] = None, debug: bool = False,
                                            **generation_kwargs) -> List[str]:
         assert len(prompts) == len(steering_vectors), "Must have one steering vector per prompt"
+        if not prompts:
+            return []
         if steering_start_positions is not None:
             assert len(steering_start_positions) == len(prompts), "Must have one steering position per prompt"
         ids, mask = self._encode(prompts)
@@ -233,6 +235,8 @@ class ModelWrapper:
 
     def generate_batch(self, prompts: List[str], max_new_tokens: int = 512, temperature: float = 0.0,
                        **generation_kwargs) -> List[str]:
+        if not prompts:
+            return []
         ids, mask = self._encode(prompts)
         new_ids = self.steered_generate_ids(ids, mask, None, None, None, None, None, max_new_tokens, temperature,
                                             **generation_kwargs)

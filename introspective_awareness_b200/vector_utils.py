@@ -159,6 +159,8 @@ def extract_concept_vectors_multi_layer(model, concept_words: List[str], baselin
     every layer fraction, detect_injected_thoughts.py:1551-1561)."""
     if extraction_method not in ("baseline", "simple", "no_baseline"):
         raise ValueError(f"Unknown extraction method: {extraction_method}")
+    if not concept_words:  # the reference's loops simply produce an empty dict
+        return {int(layer): {} for layer in layer_indices}
     concept_prompts = [_chat_prompt(model, template.format(word=w)) for w in concept_words]
     if extraction_method == "baseline":
         base_prompts = [_chat_prompt(model, template.format(word=w)) for w in baseline_words]

@@ -222,3 +222,10 @@ def test_sampling_distribution_matches_hf_warpers():
         want = torch.softmax(scores, dim=-1)
         got = Session.sampling_probs(logits, temp, k)
         assert torch.allclose(got, want, atol=1e-7) and ((got > 0) == (want > 0)).all()
+
+
+def test_empty_inputs(wrapper):
+    assert wrapper.generate_batch([], max_new_tokens=3) == []
+    assert wrapper.generate_batch_with_multi_steering([], 1, []) == []
+    assert vu.extract_concept_vectors_batch(wrapper, [], ["Sand"], layer_idx=1) == {}
+    assert grid.layer_trials([], [1.0], n_injection=3) == []
