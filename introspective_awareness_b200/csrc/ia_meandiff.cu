@@ -345,9 +345,13 @@ __global__ void __launch_bounds__(128, 4) k1_fused_kernel(RowSource<T> csrc, Row
                  warp + (int64_t)nwarps * RowBatch<T>::kRows, nwarps, o);
 }
 
-// Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.
+// Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.  Small CTAs
+// (4 warps, 32 KB of staging) so that ~7 are resident per SM: a CTA's start-up and drain (pointer
+// table -> first rows -> last adds -> store), during which it has no loads in flight, is then
+// covered by the others.
+constexpr int kSegsumStageBytes = 32 * 1024;
 template <typename T>
-__global__ void __launch_bounds__(256) k1_segsum_kernel(RowSource<T> src, int n_layers, int H, int ntiles, int nchunks,
+__global__ void __launch_bounds__(128) k1_segsum_kernel(RowSource<T> src, int n_layers, int H, int ntiles, int nchunks,
                                                         float *part /* [nchunks, n_layers, H] */, T *copy_to) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -360,26 +364,40 @@ __global__ void __launch_bounds__(256) k1_segsum_kernel(RowSource<T> src, int n_
     const int64_t r0 = (int64_t)chunk * kChunkRows;
     const int64_t r1 = r0 + kChunkRows < src.n ? r0 + kChunkRows : src.n;
     float acc[8];
-    cta_column_sum<T>(src, layer, r0, r1, H, col, active, smem, kStageBytes / 2 / (kTileCols * (int)sizeof(T)), acc,
+    cta_column_sum<T>(src, layer, r0, r1, H, col, active, smem, kSegsumStageBytes / 2 / (kTileCols * (int)sizeof(T)), acc,
                       copy_to ? copy_to + (int64_t)layer * src.n * H : nullptr);
     if (warp == 0 && active) store8<float>(part + ((int64_t)chunk * n_layers + layer) * H + col, acc);
 }
 
-// out[l, :] = part[0, l, :] + part[1, l, :] + ... in ascending chunk order (loads 8 deep, adds in order).
-__global__ void k1_chunk_reduce_kernel(const float *part, float *out, int64_t per_chunk, int nchunks) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= per_chunk) return;
-    float s = part[i];
-    int c = 1;
-    for (; c + 8 <= nchunks; c += 8) {
-        float v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = __ldg(part + (int64_t)(c + u) * per_chunk + i);
-#pragma unroll
-        for (int u = 0; u < 8; ++u) s = __fadd_rn(s, v[u]);
+// out[l, :] = part[0, l, :] + part[1, l, :] + ... in ascending chunk order.  The adds of a column are a
+// strict chain, but the loads need not be: a CTA owns 32 columns, all its threads stage up to 1024
+// chunk rows of those columns (128 B each) into shared memory at once with cp.async, then 32 threads
+// add down their column out of shared memory.
+constexpr int kCrCols = 32;
+constexpr int kCrPass = 1024;
+__global__ void __launch_bounds__(256) k1_chunk_reduce_kernel(const float *part, float *out, int64_t per_chunk, int nchunks) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    float *sm = reinterpret_cast<float *>(smem);  // [kCrPass][kCrCols]
+    const int t = threadIdx.x;
+    const int64_t col0 = (int64_t)blockIdx.x * kCrCols;
+    const int ncol = (int)((per_chunk - col0) < kCrCols ? (per_chunk - col0) : kCrCols);  // multiple of 8
+    const int q = (t & 7) * 4;  // this thread's 4 columns inside the 32
+    float s = 0.f;              // 0 + x is exact, so starting from zero equals starting from chunk 0
+    for (int c0 = 0; c0 < nchunks; c0 += kCrPass) {
+        const int n = (nchunks - c0) < kCrPass ? (nchunks - c0) : kCrPass;
+        if (q < ncol) {
+            for (int r = t >> 3; r < n; r += 32)
+                cp_async16(sm + r * kCrCols + q, part + (int64_t)(c0 + r) * per_chunk + col0 + q);
+        }
+        cp_async_drain();
+        __syncthreads();
+        if (t < ncol) {
+#pragma unroll 8
+            for (int r = 0; r < n; ++r) s = __fadd_rn(s, sm[r * kCrCols + t]);
+        }
+        __syncthreads();
     }
-    for (; c < nchunks; ++c) s = __fadd_rn(s, __ldg(part + (int64_t)c * per_chunk + i));
-    out[i] = s;
+    if (t < ncol) out[col0 + t] = s;
 }
 
 // Finalize from given column sums.  grid.y splits the concept rows.
@@ -510,14 +528,15 @@ static int run_segsum(const RowSource<T> &src, int L, int H, float *part, float 
     if (src.n == 0) return (int)cudaMemsetAsync(sum_out, 0, sizeof(float) * (size_t)L * H, s);
     const int64_t ctas = (int64_t)nch * L * ntiles;
     float *dst = nch == 1 ? sum_out : part;
-    cudaError_t e = cudaFuncSetAttribute(k1_segsum_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);
-    if (e != cudaSuccess) return (int)e;
-    k1_segsum_kernel<T><<<(unsigned)ctas, 256, kStageBytes, s>>>(src, L, H, ntiles, nch, dst, copy_to);
-    e = cudaGetLastError();
+    k1_segsum_kernel<T><<<(unsigned)ctas, 128, kSegsumStageBytes, s>>>(src, L, H, ntiles, nch, dst, copy_to);
+    cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
     if (nch > 1) {
         const int64_t per = (int64_t)L * H;
-        k1_chunk_reduce_kernel<<<(unsigned)((per + 63) / 64), 64, 0, s>>>(part, sum_out, per, nch);
+        const int cr_smem = kCrPass * kCrCols * (int)sizeof(float);
+        e = cudaFuncSetAttribute(k1_chunk_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cr_smem);
+        if (e != cudaSuccess) return (int)e;
+        k1_chunk_reduce_kernel<<<(unsigned)((per + kCrCols - 1) / kCrCols), 256, cr_smem, s>>>(part, sum_out, per, nch);
         e = cudaGetLastError();
     }
     return (int)e;
