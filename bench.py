@@ -171,7 +171,7 @@ def run_ours(args):
         """-> [50, H] device vectors for this rank's layer (inputs default to the HBM-resident copies)."""
         ci, cm, bi, bm = (c_ids, c_mask, b_ids, b_mask) if ci is None else (ci, cm, bi, bm)
         if world == 1:
-            _, vr, _ = eng.extract_vectors(ci, cm, bi, bm, [my_layer], want_f32=False)
+            _, vr, _ = eng.extract_vectors(ci, cm, bi, bm, [my_layer], want_f32=False, want_norm=False)
             return vr[0]
         # prompt-sharded: this rank forwards its slice of both prompt sets, for every layer of this step
         uniq = sorted(set(sweep))

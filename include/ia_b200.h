@@ -135,7 +135,8 @@ IA_API int ia_gemma2_tail_inject_rmsnorm(const void *mlp_out, void *residual, vo
  *               difference rounded to dtype;
  *   out_norm    [n_layers, n_out] float, may be NULL: ||out_rounded|| (fp32 accumulate, rounded
  *               to dtype), taken before normalisation.
- * normalize != 0 divides both outputs by (norm + 1e-8) as the reference does.
+ * normalize != 0 divides both outputs by (norm + 1e-8) as the reference does; with normalize == 0 and
+ * out_norm == NULL the norm pass is not launched at all (the reference's driver never normalises).
  * Baseline rows are summed sequentially in chunks of 256 (chunk sums added in order), so for
  * n_base <= 256 the mean equals torch's CPU result bit for bit.
  * workspace: at least ia_meandiff_workspace_bytes(...) bytes, 16-byte aligned; contents are

@@ -556,6 +556,7 @@ static int run_finalize(const RowSource<T> &csrc, const float *base_sum, int64_t
     k1_finalize_kernel<T><<<grid, 128, 0, s>>>(csrc, base_sum, (float)n_base, pos_sum, (float)n_pos, L, H, mode, o);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
+    if (!normalize && !out_norm) return 0;
     const int64_t rows = (int64_t)L * n_out;
     k1_norm_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(rows, H, normalize, out_norm, o);
     return (int)cudaGetLastError();
@@ -584,6 +585,7 @@ static int gather_meandiff_t(const void *const *cptrs, int64_t Tc, const int32_t
         k1_fused_kernel<T><<<(unsigned)(L * ntiles), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, o);
         e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
+        if (!normalize && !out_norm) return 0;  // nobody reads the norms: the partials stay in the workspace
         const int64_t rows = (int64_t)L * n_out;
         k1_norm_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(rows, H, normalize, out_norm, o);
         return (int)cudaGetLastError();

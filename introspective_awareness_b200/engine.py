@@ -341,7 +341,8 @@ class DecoderEngine:
 
     @torch.inference_mode()
     def extract_vectors(self, concept_ids, concept_mask, base_ids, base_mask, layer_indices: Sequence[int],
-                        mode: str = "baseline", normalize: bool = False, token_idx: int = -1, want_f32: bool = True):
+                        mode: str = "baseline", normalize: bool = False, token_idx: int = -1, want_f32: bool = True,
+                        want_norm: bool = True):
         """K1 over any number of layers: two forwards (concept batch, baseline batch — the
         reference also runs them separately, vector_utils.py:524-540) and one fused
         gather + mean-diff + norm launch.  Returns (v_f32, v_rounded, norm) on the device,
@@ -359,8 +360,9 @@ class DecoderEngine:
 
         out = kernels.gather_meandiff(
             cl, bl, mode, normalize, concept_tok=tok(cl[0].shape[1], cl[0].shape[0]),
-            base_tok=None if bl is None else tok(bl[0].shape[1], bl[0].shape[0]), want_f32=want_f32)
-        self.counters["k1_launches"] += 2  # fused gather+mean-diff kernel + norm kernel
+            base_tok=None if bl is None else tok(bl[0].shape[1], bl[0].shape[0]), want_f32=want_f32,
+            want_norm=want_norm)
+        self.counters["k1_launches"] += 2 if (want_norm or normalize) else 1  # fused kernel (+ norm pass)
         return out
 
     # -- generation ---------------------------------------------------------------------------

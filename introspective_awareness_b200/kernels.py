@@ -108,10 +108,11 @@ def workspace_bytes(n_layers: int, n_concept: int, n_base: int, hidden: int, mod
 def gather_meandiff(concept_layers: Sequence[torch.Tensor], base_layers: Optional[Sequence[torch.Tensor]],
                     mode: str = "baseline", normalize: bool = False, concept_rows=None, concept_tok=None,
                     base_rows=None, base_tok=None, n_concept: Optional[int] = None, n_base: Optional[int] = None,
-                    want_f32: bool = True, workspace: Optional[torch.Tensor] = None
-                    ) -> Tuple[Optional[torch.Tensor], torch.Tensor, torch.Tensor]:
+                    want_f32: bool = True, workspace: Optional[torch.Tensor] = None, want_norm: bool = True
+                    ) -> Tuple[Optional[torch.Tensor], torch.Tensor, Optional[torch.Tensor]]:
     """K1.  concept_layers / base_layers: one [B, T, H] residual tensor per selected layer.
-    Returns (v_f32 [L, n_out, H] or None, v_rounded [L, n_out, H] model dtype, norm [L, n_out])."""
+    Returns (v_f32 [L, n_out, H] or None, v_rounded [L, n_out, H] model dtype, norm [L, n_out] or None).
+    Without want_norm and normalize the norm pass is not launched at all."""
     first = concept_layers[0]
     dev, dtype = first.device, first.dtype
     n_layers, hid = len(concept_layers), first.shape[-1]
@@ -132,7 +133,7 @@ def gather_meandiff(concept_layers: Sequence[torch.Tensor], base_layers: Optiona
     n_out = 1 if imode == IA_MODE_POSNEG else n_concept
     out_f32 = torch.empty((n_layers, n_out, hid), dtype=torch.float32, device=dev) if want_f32 else None
     out_r = torch.empty((n_layers, n_out, hid), dtype=dtype, device=dev)
-    out_n = torch.empty((n_layers, n_out), dtype=torch.float32, device=dev)
+    out_n = torch.empty((n_layers, n_out), dtype=torch.float32, device=dev) if want_norm else None
     need = workspace_bytes(n_layers, n_concept, n_base, hid, mode)
     if workspace is None or workspace.numel() * workspace.element_size() < need:
         workspace = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
@@ -144,7 +145,7 @@ def gather_meandiff(concept_layers: Sequence[torch.Tensor], base_layers: Optiona
     rc = lib.ia_gather_meandiff(
         cptr.data_ptr(), tc, _cuda(crow, "concept_rows"), _cuda(ctok, "concept_tok"), n_concept,
         bptr.data_ptr() if bptr is not None else 0, tb, _cuda(brow, "base_rows"), _cuda(btok, "base_tok"), n_base,
-        n_layers, hid, imode, int(bool(normalize)), _cuda(out_f32, "out_f32"), out_r.data_ptr(), out_n.data_ptr(),
+        n_layers, hid, imode, int(bool(normalize)), _cuda(out_f32, "out_f32"), out_r.data_ptr(), _cuda(out_n, "out_norm"),
         workspace.data_ptr(), workspace.numel() * workspace.element_size(), _dt(first), _stream())
     check(rc, "ia_gather_meandiff")
     # keep index/pointer tensors alive until the launch is enqueued (it is, the call is synchronous on the host)

@@ -133,7 +133,7 @@ class ModelWrapper:
         """[n_layers, B, H] CPU tensor in the model dtype: one forward for all layers."""
         ids, mask = self._encode(prompts)
         _, rows, _ = self.engine.extract_vectors(ids, mask, None, None, layer_indices, mode="no_baseline",
-                                                 token_idx=token_idx, want_f32=False)
+                                                 token_idx=token_idx, want_f32=False, want_norm=False)
         return rows.cpu()
 
     def extract_concept_vectors(self, concept_prompts: List[str], baseline_prompts: Optional[List[str]],
@@ -146,7 +146,7 @@ class ModelWrapper:
         if method not in ("no_baseline", "raw"):
             bids, bmask = self._encode(baseline_prompts)
         v32, vr, _ = self.engine.extract_vectors(cids, cmask, bids, bmask, layer_indices, mode=method,
-                                                 normalize=normalize, token_idx=token_idx, want_f32=fp32)
+                                                 normalize=normalize, token_idx=token_idx, want_f32=fp32, want_norm=False)
         return (v32 if fp32 else vr).cpu()
 
     # -- generation ---------------------------------------------------------------------------

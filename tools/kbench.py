@@ -76,7 +76,7 @@ def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16):
                 us=ms * 1e3, gbs=algo / ms / 1e6)
 
 
-def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16):
+def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16, want_norm=False):
     dev = torch.device("cuda:0")
     g = torch.Generator(device=dev).manual_seed(0)
     T = 1
@@ -88,8 +88,9 @@ def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16):
     out_r = torch.empty(n_layers, C, H, dtype=dtype, device=dev)
     out_n = torch.empty(n_layers, C, dtype=torch.float32, device=dev)
     lib = _lib.load()
+    # out_norm = NULL: the production call (the driver never normalises) needs no norm pass
     args = (cptr.data_ptr(), T, 0, 0, C, bptr.data_ptr(), T, 0, 0, Nb, n_layers, H, _lib.IA_MODE_BASELINE, 0, 0,
-            out_r.data_ptr(), out_n.data_ptr(), ws.data_ptr(), ws.numel(), kernels._dt(cl[0]),
+            out_r.data_ptr(), 0 if not want_norm else out_n.data_ptr(), ws.data_ptr(), ws.numel(), kernels._dt(cl[0]),
             torch.cuda.current_stream().cuda_stream)
 
     def fn():
@@ -98,7 +99,7 @@ def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16):
 
     ms = time_launch(fn, reps, flush)
     algo = n_layers * ((C + Nb) * H * e + C * H * e)
-    return dict(kernel="k1_gather_meandiff", n_layers=n_layers, C=C, Nb=Nb, H=H, bytes=algo, us=ms * 1e3,
+    return dict(kernel="k1_gather_meandiff", n_layers=n_layers, C=C, Nb=Nb, H=H, norm_pass=want_norm, bytes=algo, us=ms * 1e3,
                 gbs=algo / ms / 1e6)
 
 
