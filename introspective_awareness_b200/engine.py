@@ -112,6 +112,10 @@ class DecoderEngine:
         p = next(model.parameters())
         self.device, self.dtype = p.device, p.dtype
         self.hidden = cfg.hidden_size
+        # the block-tail variant keeps the row in registers: 16-bit dtypes up to H = 8192, fp32 up to 2048
+        # (wider fp32 models take the unfused tail: HF post-FFN norm + add, then K2)
+        if self.dtype == torch.float32 and self.hidden > 2048 or self.hidden > 8192 or self.hidden % 128:
+            self.fuse_gemma_tail = False
         self.n_kv = cfg.num_key_value_heads
         self.head_dim = getattr(cfg, "head_dim", None) or cfg.hidden_size // cfg.num_attention_heads
         self.softcap = getattr(cfg, "final_logit_softcapping", None)
