@@ -14,6 +14,11 @@ What is stock and what is ours (north_star: "model GEMMs left to stock cuBLAS"):
 The reference drives `model.generate` with a hook (reference model_utils.py:811-847); the forward
 hook fires once for the prompt and once per cached decode step, which is exactly
 the call pattern of `Session.generate` below.
+
+Like the reference's wrapper (hooks kept on the instance, model_utils.py:136) an engine is not
+re-entrant: while one of its forwards runs it points the model's attention-function name and the
+modelling module's `apply_rotary_pos_emb` at its own implementations and restores both afterwards,
+so use one engine per model object and one thread per engine.
 """
 
 from __future__ import annotations
