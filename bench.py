@@ -258,13 +258,14 @@ def run_ours(args):
     # roofline of the dominant launch of ours: K2 over the prompt pass [rows, T_PROMPT, H]
     k2_ms = [a.elapsed_time(b) for a, b, _ in k2_events]
     H = eng.hidden
-    algo = rows * T_PROMPT * H * 2 * 4 + H * 2
+    tail = eng.fuse_gemma_tail  # Gemma-2: the block-tail variant reads mlp_out as a fifth stream and a second weight
+    algo = rows * T_PROMPT * H * 2 * (5 if tail else 4) + H * 2 * (2 if tail else 1)
     peak, peak_src = peak_hbm()
     k2_avg_ms = sum(k2_ms) / max(len(k2_ms), 1)
     achieved = algo / (k2_avg_ms * 1e6) if k2_ms else None
     # what this particular launch actually moves: only positions >= t0 read a table row and write h'
     steered_vecs = int((T_PROMPT - t0_abs.clamp(max=T_PROMPT)).sum())
-    moved = (rows * T_PROMPT * 2 + steered_vecs * 2) * H * 2 + H * 2
+    moved = (rows * T_PROMPT * (4 if tail else 2) + steered_vecs * (1 if tail else 2)) * H * 2 + H * 2
 
     h2d = sum(t.numel() * t.element_size() for t in (h_c_ids, h_c_mask, h_b_ids, h_b_mask, h_ids, h_mask)) \
         + N_CONCEPTS * H * 2 + rows * (4 + 4 + 4)
@@ -289,7 +290,7 @@ def run_ours(args):
                 "workload": f"BASELINE configs[1]: {arch} arch, {N_CONCEPTS} concepts x {len(STRENGTHS)} strengths at one "
                             f"layer, one {rows}-row steered batch per GPU, prompt {T_PROMPT} (real {T_MIN}..{T_PROMPT}, "
                             f"left-padded), {N_NEW} greedy tokens, extraction {N_CONCEPTS}+{N_BASE} prompts per step",
-                "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": args.attention,
+                "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": eng.attention,
                 "parallelism": "independent replicas, layer axis round-robin" if world > 1 else "single replica",
                 "l2": "inputs larger than L2: each step streams 16 GB of weights per decode step and ~1 GB of KV/activations",
             },
@@ -448,7 +449,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--arch", default=ARCH)
     ap.add_argument("--cpu-rows", type=int, default=2)
-    ap.add_argument("--attention", default="gqa", choices=["gqa", "hf"],
+    ap.add_argument("--attention", default="auto", choices=["auto", "gqa", "hf"],
                     help="gqa: grouped-query SDPA without repeat_kv copies; hf: the model's stock attention function")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ncu-window", action="store_true", help="cudaProfilerStart at the last timed step (for ncu)")

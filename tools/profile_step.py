@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--arch", default=bench.ARCH)
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--new-tokens", type=int, default=bench.N_NEW)
-    ap.add_argument("--attention", default="gqa", choices=["gqa", "hf"])
+    ap.add_argument("--attention", default="auto", choices=["auto", "gqa", "hf"])
     ap.add_argument("--eager-norms", action="store_true")
     ap.add_argument("--profile-phase", default="all", choices=["all", "extract", "prefill_decode"])
     args = ap.parse_args()
