@@ -85,9 +85,21 @@ def gemma2_tail_inject_rmsnorm(mlp_out: torch.Tensor, residual: torch.Tensor, w_
     return y
 
 
+_PTR_TABLES: dict = {}
+
+
 def _ptr_table(tensors: Sequence[torch.Tensor], name: str) -> torch.Tensor:
-    ptrs = [_cuda(t, name) for t in tensors]
-    return torch.tensor(ptrs, dtype=torch.int64).to(tensors[0].device, non_blocking=False)
+    """Device array of the tensors' base addresses.  Cached by value: graph-replayed forwards hand
+    back the same buffers every step, so the (synchronous) upload happens once per shape, not per call."""
+    ptrs = tuple(_cuda(t, name) for t in tensors)
+    key = (tensors[0].device, ptrs)
+    table = _PTR_TABLES.get(key)
+    if table is None:
+        if len(_PTR_TABLES) >= 64:
+            _PTR_TABLES.clear()
+        table = torch.tensor(ptrs, dtype=torch.int64).to(tensors[0].device, non_blocking=False)
+        _PTR_TABLES[key] = table
+    return table
 
 
 def _idx(x, device) -> Optional[torch.Tensor]:
