@@ -8,7 +8,9 @@
 // the critical path and no registers are tied up by loads in flight; the row lives in shared memory
 // (h' is written back in place for the second pass), so the kernel is not templated on H.
 //
-// One persistent CTA per SM; warps per CTA = what 2 stages x (row + table row) fit in 220 KB.
+// One persistent CTA per SM; warps per CTA = what two stages per warp fit in 220 KB.  A stage is the
+// residual row plus, for short launches, the table row; long launches read the table row from L2
+// with batched loads instead, which halves the stage and doubles the warps (chosen per launch).
 // Outputs leave through ordinary 64-bit stores (fire-and-forget; they never stall the warp).
 
 #include "ia_k2_common.cuh"
@@ -61,10 +63,12 @@ template <typename T> __device__ __forceinline__ RowMeta load_meta(const K2Param
     return m;
 }
 
-template <typename T, int VARIANT, bool IEEE>
+// S = stages per warp: one being consumed, S-1 being filled (prefetch distance S-1 vectors).
+// STAGE_V: the concept-table row is bulk-copied into the stage too (16 KB per stage at H = 4096);
+// otherwise it is read from L2 with batched 64-bit loads and a stage holds only the residual row.
+template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V>
 __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     extern __shared__ __align__(128) unsigned char smem[];
-    constexpr int S = 2;  // stages per warp: one being consumed, one being filled
     const int H = p.H;
     const int G = H >> 2;
     const unsigned row_bytes = (unsigned)H * sizeof(T);
@@ -74,7 +78,8 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     const unsigned bars_off = (row_bytes + 127u) & ~127u;
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem + bars_off) + warp * S;
     const unsigned stage_off = bars_off + ((unsigned)(nwarps * S * 8 + 127) & ~127u);
-    unsigned char *my_stage = smem + stage_off + (size_t)warp * S * 2 * row_bytes;
+    constexpr int kRowsPerStage = STAGE_V ? 2 : 1;
+    unsigned char *my_stage = smem + stage_off + (size_t)warp * S * kRowsPerStage * row_bytes;
 
     for (int g = threadIdx.x; g < G; g += blockDim.x)
         cp_async_group<sizeof(Pack4<T>)>(w_s + 4 * g, static_cast<const T *>(p.w) + 4 * g);
@@ -93,46 +98,77 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     auto issue = [&](int stage, int v, const RowMeta &m) {
         // one lane: arm the barrier with the byte count, then start the bulk copies
         if (lane == 0) {
-            unsigned char *dst = my_stage + (size_t)stage * 2 * row_bytes;
+            unsigned char *dst = my_stage + (size_t)stage * kRowsPerStage * row_bytes;
             fence_proxy_async();  // earlier generic-proxy accesses to this stage are done (warp synced)
-            mbar_expect_tx(&bars[stage], m.steer ? 2 * row_bytes : row_bytes);
+            const bool with_v = STAGE_V && m.steer;
+            mbar_expect_tx(&bars[stage], with_v ? 2 * row_bytes : row_bytes);
             bulk_g2s(dst, hbase + (size_t)v * H, row_bytes, &bars[stage]);
-            if (m.steer) bulk_g2s(dst + row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
+            if (with_v) bulk_g2s(dst + row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
         }
     };
 
-    RowMeta cur{};
-    if (vec < p.nvec) {
-        cur = load_meta<T>(p, vec);
-        issue(0, vec, cur);
+    // prologue: the first S-1 vectors of this warp are requested before anything else happens
+    RowMeta meta[S];  // meta[k] belongs to the vector that sits k iterations ahead (ring, rotated below)
+#pragma unroll
+    for (int k = 0; k < S - 1; ++k) {
+        const int v = vec + k * stride;
+        meta[k] = RowMeta{};
+        if (v < p.nvec) {
+            meta[k] = load_meta<T>(p, v);
+            issue(k, v, meta[k]);
+        }
     }
     cp_async_wait_all();
     __syncthreads();  // weight row staged
 
     for (int it = 0; vec < p.nvec; ++it) {
-        const int nxt = vec + stride;
-        RowMeta nm{};
-        if (nxt < p.nvec) {
-            nm = load_meta<T>(p, nxt);
-            issue((it + 1) & 1, nxt, nm);
+        const int ahead = vec + (S - 1) * stride;
+        meta[S - 1] = RowMeta{};
+        if (ahead < p.nvec) {
+            meta[S - 1] = load_meta<T>(p, ahead);
+            issue((it + S - 1) % S, ahead, meta[S - 1]);
         }
-        const int stage = it & 1;
-        mbar_wait(&bars[stage], (unsigned)(it >> 1) & 1u);
-        T *h_s = reinterpret_cast<T *>(my_stage + (size_t)stage * 2 * row_bytes);
-        const T *v_s = reinterpret_cast<const T *>(my_stage + (size_t)stage * 2 * row_bytes + row_bytes);
+        const RowMeta cur = meta[0];
+        const int stage = it % S;
+        mbar_wait(&bars[stage], (unsigned)(it / S) & 1u);
+        T *h_s = reinterpret_cast<T *>(my_stage + (size_t)stage * kRowsPerStage * row_bytes);
+        const T *v_s = reinterpret_cast<const T *>(my_stage + (size_t)stage * kRowsPerStage * row_bytes + row_bytes);
         T *hp = hbase + (size_t)vec * H;
         T *yp = ybase + (size_t)vec * H;
 
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         if (cur.steer) {
             const Injector<T, T> inj(cur.alpha);
+            if (STAGE_V) {
 #pragma unroll 4
-            for (int g = lane; g < G; g += 32) {
-                Pack4<T> x = ld4<T>(h_s + 4 * g);
-                inj.apply(x, ld4<T>(v_s + 4 * g));
-                st4<T>(hp + 4 * g, x);   // h' to HBM
-                st4<T>(h_s + 4 * g, x);  // and kept for the second pass
-                sumsq4<T>(x, a0, a1, a2, a3);
+                for (int g = lane; g < G; g += 32) {
+                    Pack4<T> x = ld4<T>(h_s + 4 * g);
+                    inj.apply(x, ld4<T>(v_s + 4 * g));
+                    st4<T>(hp + 4 * g, x);   // h' to HBM
+                    st4<T>(h_s + 4 * g, x);  // and kept for the second pass
+                    sumsq4<T>(x, a0, a1, a2, a3);
+                }
+            } else {
+                // table row straight from L2, 8 loads in flight per lane (the stores below would
+                // otherwise keep the compiler from hoisting them)
+                const T *vp = vtab + (size_t)cur.vi * H;
+                for (int g0 = lane; g0 < G; g0 += 32 * 8) {
+                    Pack4<T> vv[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (g0 + 32 * u < G) vv[u] = ld4_ro<T>(vp + 4 * (g0 + 32 * u));
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int g = g0 + 32 * u;
+                        if (g < G) {
+                            Pack4<T> x = ld4<T>(h_s + 4 * g);
+                            inj.apply(x, vv[u]);
+                            st4<T>(hp + 4 * g, x);
+                            st4<T>(h_s + 4 * g, x);
+                            sumsq4<T>(x, a0, a1, a2, a3);
+                        }
+                    }
+                }
             }
         } else {
 #pragma unroll 4
@@ -146,25 +182,27 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
             st4<T>(yp + 4 * g, out);
         }
         fence_proxy_async();  // this lane's shared-memory accesses are ordered before later bulk copies
-        __syncwarp();         // every lane is done with this stage before it is refilled two iterations on
-        vec = nxt;
-        cur = nm;
+        __syncwarp();         // every lane is done with this stage before it is refilled S-1 iterations on
+        vec += stride;
+#pragma unroll
+        for (int k = 0; k + 1 < S; ++k) meta[k] = meta[k + 1];
     }
 }
 
-template <typename T, int VARIANT, bool IEEE> static int launch_tma(const K2Params &p, cudaStream_t s) {
+template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V> static int launch_tma(const K2Params &p, cudaStream_t s) {
     const size_t row_bytes = (size_t)p.H * sizeof(T);
     const size_t budget = 220 * 1024;
-    if (row_bytes + 1024 + 4 * row_bytes > budget) return IA_ERR_TOO_LARGE;
-    int nwarps = (int)((budget - row_bytes - 1024) / (4 * row_bytes));
+    constexpr int kRowsPerStage = STAGE_V ? 2 : 1;
+    if (row_bytes + 1024 + kRowsPerStage * S * row_bytes > budget) return IA_ERR_TOO_LARGE;
+    int nwarps = (int)((budget - row_bytes - 1024) / (kRowsPerStage * S * row_bytes));
     if (nwarps > 16) nwarps = 16;
     const int sms = sm_count();
     // small problems: do not start more warps than there are vectors per SM
     const int per_sm = (p.nvec + sms - 1) / sms;
     if (nwarps > per_sm) nwarps = per_sm < 1 ? 1 : per_sm;
     const size_t bars_off = (row_bytes + 127) & ~(size_t)127;
-    const size_t smem = bars_off + (((size_t)nwarps * 2 * 8 + 127) & ~(size_t)127) + (size_t)nwarps * 4 * row_bytes;
-    auto kern = k2_tma_kernel<T, VARIANT, IEEE>;
+    const size_t smem = bars_off + (((size_t)nwarps * S * 8 + 127) & ~(size_t)127) + (size_t)nwarps * kRowsPerStage * S * row_bytes;
+    auto kern = k2_tma_kernel<T, VARIANT, IEEE, S, STAGE_V>;
     // opt in to large dynamic shared memory once per instantiation and device (first call = a warm-up
     // call, i.e. not under stream capture)
     static bool configured[64] = {false};
@@ -182,10 +220,19 @@ template <typename T, int VARIANT, bool IEEE> static int launch_tma(const K2Para
     return (int)cudaGetLastError();
 }
 
-template <typename T> static int tma_flags(const K2Params &p, int variant, int flags, cudaStream_t s) {
+template <typename T, int S, bool STAGE_V> static int tma_flags_s(const K2Params &p, int variant, int flags, cudaStream_t s) {
     const bool ieee = (flags & IA_RSQRT_IEEE) != 0;
-    if (variant == IA_NORM_GEMMA) return ieee ? launch_tma<T, IA_NORM_GEMMA, true>(p, s) : launch_tma<T, IA_NORM_GEMMA, false>(p, s);
-    return ieee ? launch_tma<T, IA_NORM_LLAMA, true>(p, s) : launch_tma<T, IA_NORM_LLAMA, false>(p, s);
+    if (variant == IA_NORM_GEMMA)
+        return ieee ? launch_tma<T, IA_NORM_GEMMA, true, S, STAGE_V>(p, s) : launch_tma<T, IA_NORM_GEMMA, false, S, STAGE_V>(p, s);
+    return ieee ? launch_tma<T, IA_NORM_LLAMA, true, S, STAGE_V>(p, s) : launch_tma<T, IA_NORM_LLAMA, false, S, STAGE_V>(p, s);
+}
+
+template <typename T> static int tma_flags(const K2Params &p, int variant, int flags, cudaStream_t s) {
+    // Long launches: table rows come from L2 and a stage holds only the residual row, which doubles the
+    // warps per SM (12 at H = 4096) — measured 1.29 vs 1.18 of the copy-bandwidth peak at 262 144 vectors.
+    // Short launches are latency-bound: there the table row rides in the stage (10.4 vs 12.9 us at 200).
+    if (p.nvec >= 8192) return tma_flags_s<T, 2, false>(p, variant, flags, s);
+    return tma_flags_s<T, 2, true>(p, variant, flags, s);
 }
 
 int launch_k2_tma(const K2Params &p, int dtype, int vec_dtype, int variant, int flags, cudaStream_t s) {
