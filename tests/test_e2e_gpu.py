@@ -261,3 +261,75 @@ def test_sweep_driver_end_to_end(tmp_path):
                                                  max_new_tokens=6, temperature=0.0,
                                                  steering_start_positions=[t for _, t in built])
     assert texts == [r["response"] for r in inj]
+
+
+@pytest.mark.parametrize("arch", ["tiny-llama", "tiny-gemma2", "llama-8b-4layer"])
+def test_runtime_optimisations_do_not_change_bits(arch):
+    """K2 for every RMSNorm, the fused rotary kernel, the Gemma-2 tail variant, grouped-query SDPA, the
+    CUDA graphs and both K2 implementations, each switched off in turn: same logits, bit for bit (Gemma-2's
+    head_dim 256 grouped-query path excepted, see above)."""
+    from introspective_awareness_b200.synthetic import synthetic_prompt_ids
+
+    w = _wrapper(arch, torch.bfloat16, 9 if arch.startswith("tiny") else None, attention="hf")
+    V = w.model.config.vocab_size
+    rows = 40
+    ids, mask, lens = synthetic_prompt_ids(rows, 48, 32, V, seed=2)
+    table = (torch.randn(8, w.engine.hidden, generator=torch.Generator().manual_seed(3)) * 0.5).to(torch.bfloat16)
+    t0 = (lens - 20).tolist()
+    row_vec = [i % 9 - 1 for i in range(rows)]  # includes control rows
+    alphas = [[1.0, 3.0, 8.0][i % 3] for i in range(rows)]
+    eng = w.engine
+
+    def run():
+        eng._session = None
+        out = w.steered_generate_ids(ids, mask, 1, table, row_vec, alphas, t0, 12, keep_logits=True).cpu().clone()
+        return out, torch.stack(w.last_session.step_logits).cpu()
+
+    base_ids, base_logits = run()
+    settings = [("fused_norms", False), ("fused_rope", False), ("graph_decode", False)]
+    if eng.is_gemma2:
+        settings.append(("fuse_gemma_tail", False))
+    else:
+        settings.append(("attention", "gqa"))
+    for name, value in settings:
+        if name == "graph_decode":
+            orig_session = eng.session
+            eng.session = lambda *a, **k: orig_session(*a, **{**k, "use_graphs": False})
+        elif name == "attention":
+            from introspective_awareness_b200 import engine as E
+
+            E._register_attention()
+            old = eng.attention
+            eng.attention = value
+        else:
+            old = getattr(eng, name)
+            setattr(eng, name, value)
+        try:
+            got_ids, got_logits = run()
+        finally:
+            if name == "graph_decode":
+                eng.session = orig_session
+            elif name == "attention":
+                eng.attention = old
+            else:
+                setattr(eng, name, old)
+        assert torch.equal(got_logits, base_logits), name
+        assert torch.equal(got_ids, base_ids), name
+
+
+def test_fp16_model_against_hook_path():
+    """fp16 residual stream: K2 / rope fp16 paths inside the runtime."""
+    from introspective_awareness_b200.model_utils import ModelWrapper
+    from introspective_awareness_b200.synthetic import synthetic_prompt_ids
+
+    w = ModelWrapper.from_arch("tiny-qwen2", device=_dev(), dtype=torch.float16, seed=4)
+    V = w.model.config.vocab_size
+    ids, mask, lens = synthetic_prompt_ids(24, 40, 30, V, seed=6)
+    table = (torch.randn(6, w.engine.hidden, generator=torch.Generator().manual_seed(1)) * 0.5).to(torch.float16)
+    t0 = (lens - 12).tolist()
+    row_vec = [i % 6 for i in range(24)]
+    ours = w.steered_generate_ids(ids, mask, 2, table, row_vec, [4.0] * 24, t0, 16, keep_logits=True).cpu()
+    ol = torch.stack(w.last_session.step_logits).cpu()
+    ref = ref_hooks.steered_generate(w.model, ids, mask, 2, [table[j] for j in row_vec], 4.0, t0, 16, want_logits=True)
+    assert (ol - ref["logits"]).abs().max().item() <= 2e-2
+    assert torch.equal(ours, ref["new_ids"])
