@@ -23,12 +23,31 @@ so use one engine per model object and one thread per engine.
 
 from __future__ import annotations
 
+import contextlib
+import gc
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 
 from . import kernels
+
+
+@contextlib.contextmanager
+def _no_gc_during_capture():
+    """Keep Python's cyclic collector out of a stream capture.  An older Session (graphs, pooled
+    buffers) that is only reachable through a reference cycle is finalised whenever the collector
+    happens to run; if that is inside a capture, destroying its CUDA graphs is an operation the
+    capture forbids and the capture is invalidated (torch.cuda.graph no longer collects up front).
+    So: collect once before capturing, and hold the collector off until the capture has ended."""
+    was_enabled = gc.isenabled()
+    gc.collect()
+    gc.disable()
+    try:
+        yield
+    finally:
+        if was_enabled:
+            gc.enable()
 
 
 ATTN_GQA = "ia_b200_gqa_sdpa"
@@ -345,7 +364,7 @@ class DecoderEngine:
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             before = dict(self.counters)
-            with torch.cuda.graph(g):
+            with _no_gc_during_capture(), torch.cuda.graph(g):
                 outs = self._capture_layers_eager(ids_s, mask_s, layer_indices, padded)
             g.ia_launches = {k: self.counters[k] - before[k] for k in before}
             for k in before:
@@ -466,18 +485,19 @@ class Session:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         graphs = []
-        for s in range(1, self.N):
-            g = torch.cuda.CUDAGraph()
-            before = dict(self.eng.counters)
-            with torch.cuda.graph(g, pool=self.pool):
-                self._step(s, steer, greedy, eos, pad)
-            # launches recorded into this graph (they did not run): credited on every replay instead
-            g.ia_launches = {k: self.eng.counters[k] - before[k] for k in before}
-            for k in before:
-                self.eng.counters[k] = before[k]
-            if self.pool is None:
-                self.pool = g.pool()
-            graphs.append(g)
+        with _no_gc_during_capture():
+            for s in range(1, self.N):
+                g = torch.cuda.CUDAGraph()
+                before = dict(self.eng.counters)
+                with torch.cuda.graph(g, pool=self.pool):
+                    self._step(s, steer, greedy, eos, pad)
+                # launches recorded into this graph (they did not run): credited on every replay instead
+                g.ia_launches = {k: self.eng.counters[k] - before[k] for k in before}
+                for k in before:
+                    self.eng.counters[k] = before[k]
+                if self.pool is None:
+                    self.pool = g.pool()
+                graphs.append(g)
         self.graphs[gkey] = graphs
         return graphs
 

@@ -1,0 +1,135 @@
+// A host with no Python and no torch: dlopen()s libia_b200.so, allocates with the CUDA runtime only and
+// drives K2 (fp32, IEEE rsqrt) and K1 (caller workspace and the built-in static scratch) through the C ABI,
+// checking the results against a scalar CPU restatement of the same arithmetic and summation orders.
+// Build: nvcc -O2 -o abi_demo abi_demo.cpp -ldl ; run: ./abi_demo <path-to-libia_b200.so>
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/ia_b200.h"
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); return 2; } } while (0)
+
+static uint32_t rng_state = 12345u;
+static float frand() {  // LCG -> roughly N(0,1)-ish uniform in [-2, 2)
+    rng_state = rng_state * 1664525u + 1013904223u;
+    return ((rng_state >> 8) / 16777216.0f) * 4.0f - 2.0f;
+}
+
+// canonical K2 variance order (see oracle/kernels_np.py:row_sum_squares), fp32
+static float row_sumsq(const float *x, int H) {
+    float lane[32];
+    int G = H / 4, per_lane = (G + 31) / 32;
+    for (int l = 0; l < 32; ++l) {
+        float a[4] = {0, 0, 0, 0};
+        for (int j = 0; j < per_lane; ++j) {
+            int g = l + 32 * j;
+            if (g < G) for (int i = 0; i < 4; ++i) { volatile float sq = x[4 * g + i] * x[4 * g + i]; a[i] = a[i] + sq; }
+        }
+        lane[l] = ((a[0] + a[1]) + a[2]) + a[3];
+    }
+    for (int off = 16; off > 0; off >>= 1) for (int l = 0; l + off < 32; ++l) lane[l] = lane[l] + lane[l + off];
+    return lane[0];
+}
+
+int main(int argc, char **argv) {
+    if (argc < 2) { printf("usage: abi_demo <libia_b200.so>\n"); return 2; }
+    void *lib = dlopen(argv[1], RTLD_NOW);
+    if (!lib) { printf("dlopen failed: %s\n", dlerror()); return 2; }
+    typedef int (*inject_fn)(void *, void *, const void *, const int32_t *, const float *, const int32_t *, const void *, float,
+                             int64_t, int64_t, int64_t, int32_t, int32_t, int32_t, int32_t, int32_t, void *);
+    typedef int (*k1_fn)(const void *const *, int64_t, const int32_t *, const int32_t *, int64_t, const void *const *, int64_t,
+                         const int32_t *, const int32_t *, int64_t, int64_t, int64_t, int32_t, int32_t, float *, void *, float *,
+                         void *, int64_t, int32_t, void *);
+    typedef int (*k1s_fn)(const void *const *, int64_t, const int32_t *, const int32_t *, int64_t, const void *const *, int64_t,
+                          const int32_t *, const int32_t *, int64_t, int64_t, int64_t, int32_t, int32_t, float *, void *, float *,
+                          int32_t, void *);
+    typedef int64_t (*ws_fn)(int64_t, int64_t, int64_t, int64_t, int32_t);
+    typedef int (*ver_fn)(void);
+    inject_fn inject = (inject_fn)dlsym(lib, "ia_inject_rmsnorm");
+    k1_fn k1 = (k1_fn)dlsym(lib, "ia_gather_meandiff");
+    k1s_fn k1s = (k1s_fn)dlsym(lib, "ia_gather_meandiff_static");
+    ws_fn wsb = (ws_fn)dlsym(lib, "ia_meandiff_workspace_bytes");
+    ver_fn ver = (ver_fn)dlsym(lib, "ia_version");
+    if (!inject || !k1 || !k1s || !wsb || !ver || ver() != IA_ABI_VERSION) { printf("missing symbols\n"); return 2; }
+
+    // ---------------- K2: 6 rows x 3 positions x H=512, fp32 ----------------
+    const int rows = 6, T = 3, H = 512, NV = 2;
+    const float eps = 1e-5f;
+    size_t n = (size_t)rows * T * H;
+    float *h = (float *)malloc(n * 4), *w = (float *)malloc(H * 4), *vt = (float *)malloc(NV * H * 4);
+    float *want_h = (float *)malloc(n * 4), *want_y = (float *)malloc(n * 4), *got_h = (float *)malloc(n * 4), *got_y = (float *)malloc(n * 4);
+    for (size_t i = 0; i < n; ++i) h[i] = frand();
+    for (int i = 0; i < H; ++i) w[i] = 1.0f + 0.1f * frand();
+    for (int i = 0; i < NV * H; ++i) vt[i] = 0.3f * frand();
+    int32_t row_vec[rows] = {0, 1, -1, 0, 1, 0};
+    float alpha[rows] = {1.f, 2.f, 4.f, 3.f, 0.37f, 8.f};
+    int32_t t0[rows] = {0, 1, 0, 2, 3, 1};
+    for (int b = 0; b < rows; ++b) for (int p = 0; p < T; ++p) {
+        const float *x = h + ((size_t)b * T + p) * H;
+        float *xo = want_h + ((size_t)b * T + p) * H, *yo = want_y + ((size_t)b * T + p) * H;
+        bool steer = row_vec[b] >= 0 && p >= t0[b];
+        for (int i = 0; i < H; ++i) { volatile float sv = steer ? vt[row_vec[b] * H + i] * alpha[b] : 0.0f; xo[i] = steer ? x[i] + sv : x[i]; }
+        volatile float var = row_sumsq(xo, H) * (1.0f / (float)H);
+        volatile float t = var + eps;
+        volatile float r = 1.0f / sqrtf(t);
+        for (int i = 0; i < H; ++i) { volatile float nrm = xo[i] * r; yo[i] = w[i] * nrm; }
+    }
+    float *dh, *dy, *dw, *dvt, *dal; int32_t *drv, *dt0;
+    CK(cudaMalloc(&dh, n * 4)); CK(cudaMalloc(&dy, n * 4)); CK(cudaMalloc(&dw, H * 4)); CK(cudaMalloc(&dvt, NV * H * 4));
+    CK(cudaMalloc(&dal, rows * 4)); CK(cudaMalloc(&drv, rows * 4)); CK(cudaMalloc(&dt0, rows * 4));
+    CK(cudaMemcpy(dh, h, n * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dw, w, H * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dvt, vt, NV * H * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dal, alpha, rows * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(drv, row_vec, rows * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dt0, t0, rows * 4, cudaMemcpyHostToDevice));
+    cudaStream_t st; CK(cudaStreamCreate(&st));
+    int rc = inject(dh, dy, dvt, drv, dal, dt0, dw, eps, rows, T, H, 0, IA_F32, IA_F32, IA_NORM_LLAMA, IA_RSQRT_IEEE, st);
+    if (rc) { printf("ia_inject_rmsnorm rc=%d\n", rc); return 1; }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaMemcpy(got_h, dh, n * 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(got_y, dy, n * 4, cudaMemcpyDeviceToHost));
+    if (memcmp(got_h, want_h, n * 4) || memcmp(got_y, want_y, n * 4)) { printf("K2 mismatch\n"); return 1; }
+    if (inject(dh, dy, dvt, drv, dal, dt0, dw, eps, rows, T, 510, 0, IA_F32, IA_F32, IA_NORM_LLAMA, 0, st) != IA_ERR_SHAPE) { printf("bad H accepted\n"); return 1; }
+
+    // ---------------- K1: 2 layers, 3 concept rows, 10 baseline rows, H=256, fp32, token = last ----------------
+    const int L = 2, C = 3, NB = 10, HK = 256, TK = 2;
+    float *conc[L], *base[L], *dconc[L], *dbase[L];
+    for (int l = 0; l < L; ++l) {
+        conc[l] = (float *)malloc((size_t)C * TK * HK * 4); base[l] = (float *)malloc((size_t)NB * TK * HK * 4);
+        for (int i = 0; i < C * TK * HK; ++i) conc[l][i] = 5.0f + 3.0f * frand();
+        for (int i = 0; i < NB * TK * HK; ++i) base[l][i] = 5.0f + 3.0f * frand();
+        CK(cudaMalloc(&dconc[l], (size_t)C * TK * HK * 4)); CK(cudaMalloc(&dbase[l], (size_t)NB * TK * HK * 4));
+        CK(cudaMemcpy(dconc[l], conc[l], (size_t)C * TK * HK * 4, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(dbase[l], base[l], (size_t)NB * TK * HK * 4, cudaMemcpyHostToDevice));
+    }
+    void **dcp, **dbp; CK(cudaMalloc(&dcp, L * sizeof(void *))); CK(cudaMalloc(&dbp, L * sizeof(void *)));
+    CK(cudaMemcpy(dcp, dconc, L * sizeof(void *), cudaMemcpyHostToDevice)); CK(cudaMemcpy(dbp, dbase, L * sizeof(void *), cudaMemcpyHostToDevice));
+    float *want_v = (float *)malloc((size_t)L * C * HK * 4), *got_v = (float *)malloc((size_t)L * C * HK * 4);
+    for (int l = 0; l < L; ++l) for (int j = 0; j < HK; ++j) {
+        float s = 0.f;
+        for (int r = 0; r < NB; ++r) s = s + base[l][((size_t)r * TK + (TK - 1)) * HK + j];  // sequential row order
+        volatile float mean = s / (float)NB;
+        for (int c = 0; c < C; ++c) want_v[((size_t)l * C + c) * HK + j] = conc[l][((size_t)c * TK + (TK - 1)) * HK + j] - mean;
+    }
+    float *dout; CK(cudaMalloc(&dout, (size_t)L * C * HK * 4));
+    int64_t need = wsb(L, C, NB, HK, IA_MODE_BASELINE);
+    void *dws; CK(cudaMalloc(&dws, need));
+    rc = k1((const void *const *)dcp, TK, NULL, NULL, C, (const void *const *)dbp, TK, NULL, NULL, NB, L, HK, IA_MODE_BASELINE, 0,
+            NULL, dout, NULL, dws, need, IA_F32, st);
+    if (rc) { printf("ia_gather_meandiff rc=%d\n", rc); return 1; }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaMemcpy(got_v, dout, (size_t)L * C * HK * 4, cudaMemcpyDeviceToHost));
+    if (memcmp(got_v, want_v, (size_t)L * C * HK * 4)) { printf("K1 mismatch\n"); return 1; }
+    // the variant for hosts that cannot allocate: same answer with no workspace argument
+    CK(cudaMemset(dout, 0, (size_t)L * C * HK * 4));
+    rc = k1s((const void *const *)dcp, TK, NULL, NULL, C, (const void *const *)dbp, TK, NULL, NULL, NB, L, HK, IA_MODE_BASELINE, 0,
+             NULL, dout, NULL, IA_F32, st);
+    if (rc) { printf("ia_gather_meandiff_static rc=%d\n", rc); return 1; }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaMemcpy(got_v, dout, (size_t)L * C * HK * 4, cudaMemcpyDeviceToHost));
+    if (memcmp(got_v, want_v, (size_t)L * C * HK * 4)) { printf("K1 static mismatch\n"); return 1; }
+    printf("abi_demo ok: K2 and K1 bit-exact against the scalar C restatement, called without Python or torch\n");
+    return 0;
+}

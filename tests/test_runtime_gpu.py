@@ -32,3 +32,39 @@ def test_fused_rope_is_bit_identical_to_hf(dtype, B, T, nh, nkv, D):
     # a layout the kernel does not cover is declined, not mis-read
     if T > 1 and nh > 1:
         assert kernels.rope(q.contiguous(), k, cos, sin) is None
+
+
+def test_graph_capture_survives_a_garbage_collection_of_older_sessions(monkeypatch):
+    """Old sessions die through the cyclic collector, whenever it happens to run; finalising their CUDA
+    graphs inside a new capture invalidates it.  Arrange exactly that: let a used wrapper become
+    garbage while collection is held off, then make the collector eager from the moment the next
+    capture begins.  The engine must have collected beforehand and must keep the collector out."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    import gc
+
+    from introspective_awareness_b200.model_utils import ModelWrapper
+    from introspective_awareness_b200.synthetic import synthetic_prompt_ids
+
+    def run_once(rows):
+        w = ModelWrapper.from_arch("tiny-llama", device="cuda:0", dtype=torch.bfloat16, seed=2)
+        ids, mask, _ = synthetic_prompt_ids(rows, 12, 6, 512, seed=3)
+        table = torch.randn(2, 128, generator=torch.Generator().manual_seed(0)).to(torch.bfloat16)
+        return w.steered_generate_ids(ids, mask, 1, table, [0, 1] * (rows // 2), [4.0] * rows, [0] * rows, 6).cpu().clone()
+
+    old = gc.get_threshold()
+    real_begin = torch.cuda.CUDAGraph.capture_begin
+
+    def eager_collector_begin(self, *a, **k):
+        real_begin(self, *a, **k)
+        gc.set_threshold(1, 1, 1)
+
+    try:
+        gc.collect()
+        gc.set_threshold(10 ** 9, 10 ** 9, 10 ** 9)   # nothing is collected on its own from here on
+        first = run_once(4)                           # wrapper, engine, session and 5 graphs are now garbage
+        monkeypatch.setattr(torch.cuda.CUDAGraph, "capture_begin", eager_collector_begin)
+        second = run_once(6)
+        assert first.shape == (4, 6) and second.shape == (6, 6)
+    finally:
+        gc.set_threshold(*old)
