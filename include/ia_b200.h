@@ -212,6 +212,42 @@ IA_API int ia_meandiff_finalize(const void *concept_acts, int64_t n_concept, con
 IA_API int ia_rope(const void *q, const void *k, const void *cosv, const void *sinv, void *q_out, void *k_out,
             int64_t tokens, int64_t n_heads, int64_t n_kv_heads, int64_t head_dim, int32_t dtype, void *stream);
 
+/*
+ * K2 with the decoder layer's residual add folded in:
+ *     h <- round(h + add);  h <- round(h + round(v*alpha)) where steered;  y <- rmsnorm(h; w)
+ * `add` [rows, T, H] is the branch output (attention or MLP) the layer adds to the residual stream
+ * just before the norm — transformers' `hidden_states = residual + hidden_states`
+ * (modeling_llama.py LlamaDecoderLayer.forward), which the reference runs between its hook
+ * (model_utils.py:767-788) and the next RMSNorm.  Everything else as ia_inject_rmsnorm (same
+ * rounding points, same summation order, same flags); h is rewritten for every vector.
+ */
+IA_API int ia_add_inject_rmsnorm(void *h, const void *add, void *y, const void *vtable, const int32_t *row_vec,
+                          const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
+                          int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype,
+                          int32_t vec_dtype, int32_t variant, int32_t flags, void *stream);
+
+/*
+ * Runtime support: ia_rope plus the KV-cache append in the same launch.  q/k/v are [tokens, heads, head_dim]
+ * with their own token-row strides in elements (they may be slices of one fused projection output);
+ * q_out is dense [tokens, n_heads, head_dim]; rotated k and plain v are written to
+ * dst + b*dst_batch_stride + head*dst_head_stride + (pos0 + t)*dst_pos_stride, b = token / tokens_per_row,
+ * t = token % tokens_per_row — what transformers does with `past_key_values.update(...)` after
+ * apply_rotary_pos_emb (modeling_llama.py LlamaAttention.forward).  Bit-identical to those ops.
+ */
+IA_API int ia_rope_append(const void *q, const void *k, const void *v, int64_t q_row_stride, int64_t k_row_stride,
+                   int64_t v_row_stride, const void *cosv, const void *sinv, void *q_out, void *k_dst, void *v_dst,
+                   int64_t dst_batch_stride, int64_t dst_head_stride, int64_t dst_pos_stride, int64_t tokens,
+                   int64_t tokens_per_row, int64_t pos0, int64_t n_heads, int64_t n_kv_heads, int64_t head_dim,
+                   int32_t dtype, void *stream);
+
+/*
+ * Runtime support: out = round(round(silu(gate)) * up) over [rows, width], the two eager kernels of
+ * transformers' LlamaMLP.forward (`act_fn(gate_proj(x)) * up_proj(x)`) in one pass with both rounding
+ * points kept; gate/up have their own row strides in elements, out is dense.  Bit-identical.
+ */
+IA_API int ia_silu_mul(const void *gate, const void *up, void *out, int64_t rows, int64_t width, int64_t gate_row_stride,
+                int64_t up_row_stride, int32_t dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,6 +43,12 @@ _SIGNATURES = {
                                           c_void_p, c_int32, c_void_p]),
     "ia_rope": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                         c_int32, c_void_p]),
+    "ia_add_inject_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                      c_int64, c_int64, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p]),
+    "ia_rope_append": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
+                               c_int32, c_void_p]),
+    "ia_silu_mul": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32, c_void_p]),
 }
 IA_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024
 

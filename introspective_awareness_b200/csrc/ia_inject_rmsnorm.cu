@@ -165,12 +165,12 @@ __global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
         const VT *vp = static_cast<const VT *>(p.vtable) + (size_t)(steer ? vi : 0) * H;
         const Injector<T, VT> inj(alpha);
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        const T *ap = p.add ? static_cast<const T *>(p.add) + (size_t)vec * H : nullptr;
         for (int g = lane; g < G; g += 32) {
             Pack4<T> x = ld4<T>(hp + 4 * g);
-            if (steer) {
-                inj.apply(x, ld4_ro<VT>(vp + 4 * g));
-                st4<T>(hp + 4 * g, x);
-            }
+            if (ap) add4<T>(x, ld4_ro<T>(ap + 4 * g));
+            if (steer) inj.apply(x, ld4_ro<VT>(vp + 4 * g));
+            if (steer || ap) st4<T>(hp + 4 * g, x);
             sumsq4<T>(x, a0, a1, a2, a3);
         }
         const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
@@ -219,11 +219,14 @@ static int dispatch_h(const K2Params &p, cudaStream_t s) {
     const int per_lane = ((p.H >> 2) + 31) / 32;
     constexpr bool wide = sizeof(T) == 4;
     const bool even = (p.H & 127) == 0;  // the register kernel wants the same group count on every lane
-    if (!even) {
+    if (p.add) {
+        // residual-add form: bulk-copy kernel or this two-pass kernel only
+        if (TAIL) return IA_ERR_SHAPE;
+    } else if (!even) {
         if (TAIL) return IA_ERR_SHAPE;
     } else if (per_lane <= 8) return launch_regs<T, VT, 8, VARIANT, IEEE, TAIL, wide ? 4 : 8>(p, s);
     else if (per_lane <= 16) return launch_regs<T, VT, 16, VARIANT, IEEE, TAIL, wide ? 3 : 6>(p, s);
-    if constexpr (!wide) if (even) {
+    if constexpr (!wide) if (even && !p.add) {
         // one CTA fewer per SM when extra registers are live (fp32 table groups, Gemma-2 tail)
         constexpr int D = (TAIL || sizeof(VT) == 4) ? 1 : 0;
         if (per_lane <= 28) return launch_regs<T, VT, 28, VARIANT, IEEE, TAIL, 5 - D>(p, s);
@@ -318,4 +321,30 @@ extern "C" int ia_gemma2_tail_inject_rmsnorm(const void *mlp_out, void *residual
     p.row_t0 = row_t0; p.w = w_next; p.w_post = w_post; p.eps = eps; p.inv_h = 1.0f / (float)H;
     p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
     return dispatch_dtype<true>(p, dtype, vec_dtype, IA_NORM_GEMMA, flags, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ia_add_inject_rmsnorm(void *h, const void *add, void *y, const void *vtable, const int32_t *row_vec,
+                                     const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
+                                     int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype,
+                                     int32_t vec_dtype, int32_t variant, int32_t flags, void *stream) {
+    using namespace ia;
+    if (!add) return IA_ERR_NULL;
+    int rc = check_common(h, y, vtable, row_vec, row_alpha, row_t0, w, rows, T, H, flags);
+    if (rc) return rc;
+    if (!aligned16(add)) return IA_ERR_ALIGN;
+    if (variant != IA_NORM_LLAMA && variant != IA_NORM_GEMMA) return IA_ERR_DTYPE;
+    if (rows == 0) return 0;
+    K2Params p{};
+    p.h = h; p.y = y; p.mlp = nullptr; p.add = add; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
+    p.row_t0 = row_t0; p.w = w; p.w_post = nullptr; p.eps = eps; p.inv_h = 1.0f / (float)H;
+    p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
+    // two staged rows per stage and two stages must fit next to the weight row
+    const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
+    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 5 + 1024 <= 220 * 1024;
+    if (flags & IA_IMPL_TMA) {
+        if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
+    }
+    if (tma_ok && !(flags & IA_IMPL_REGS))
+        return launch_k2_tma(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
+    return dispatch_dtype<false>(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
 }

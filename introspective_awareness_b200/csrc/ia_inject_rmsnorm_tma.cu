@@ -66,7 +66,9 @@ template <typename T> __device__ __forceinline__ RowMeta load_meta(const K2Param
 // S = stages per warp: one being consumed, S-1 being filled (prefetch distance S-1 vectors).
 // STAGE_V: the concept-table row is bulk-copied into the stage too (16 KB per stage at H = 4096);
 // otherwise it is read from L2 with batched 64-bit loads and a stage holds only the residual row.
-template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V>
+// ADD: a second [nvec, H] input (the branch output of the decoder layer) is staged next to the
+// residual row and added first, h = rd(h + add); h' is then written for every vector.
+template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, bool ADD>
 __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int H = p.H;
@@ -78,7 +80,7 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     const unsigned bars_off = (row_bytes + 127u) & ~127u;
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem + bars_off) + warp * S;
     const unsigned stage_off = bars_off + ((unsigned)(nwarps * S * 8 + 127) & ~127u);
-    constexpr int kRowsPerStage = STAGE_V ? 2 : 1;
+    constexpr int kRowsPerStage = 1 + (ADD ? 1 : 0) + (STAGE_V ? 1 : 0);
     unsigned char *my_stage = smem + stage_off + (size_t)warp * S * kRowsPerStage * row_bytes;
 
     for (int g = threadIdx.x; g < G; g += blockDim.x)
@@ -92,6 +94,7 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     T *hbase = static_cast<T *>(p.h);
     T *ybase = static_cast<T *>(p.y);
     const T *vtab = static_cast<const T *>(p.vtable);
+    const T *abase = static_cast<const T *>(p.add);
     const int stride = gridDim.x * nwarps;
     int vec = blockIdx.x * nwarps + warp;
 
@@ -101,9 +104,10 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
             unsigned char *dst = my_stage + (size_t)stage * kRowsPerStage * row_bytes;
             fence_proxy_async();  // earlier generic-proxy accesses to this stage are done (warp synced)
             const bool with_v = STAGE_V && m.steer;
-            mbar_expect_tx(&bars[stage], with_v ? 2 * row_bytes : row_bytes);
+            mbar_expect_tx(&bars[stage], (1u + (ADD ? 1u : 0u) + (with_v ? 1u : 0u)) * row_bytes);
             bulk_g2s(dst, hbase + (size_t)v * H, row_bytes, &bars[stage]);
-            if (with_v) bulk_g2s(dst + row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
+            if (ADD) bulk_g2s(dst + row_bytes, abase + (size_t)v * H, row_bytes, &bars[stage]);
+            if (with_v) bulk_g2s(dst + (ADD ? 2 : 1) * row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
         }
     };
 
@@ -132,7 +136,8 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
         const int stage = it % S;
         mbar_wait(&bars[stage], (unsigned)(it / S) & 1u);
         T *h_s = reinterpret_cast<T *>(my_stage + (size_t)stage * kRowsPerStage * row_bytes);
-        const T *v_s = reinterpret_cast<const T *>(my_stage + (size_t)stage * kRowsPerStage * row_bytes + row_bytes);
+        const T *a_s = reinterpret_cast<const T *>(reinterpret_cast<unsigned char *>(h_s) + row_bytes);  // ADD only
+        const T *v_s = reinterpret_cast<const T *>(reinterpret_cast<unsigned char *>(h_s) + (ADD ? 2 : 1) * row_bytes);
         T *hp = hbase + (size_t)vec * H;
         T *yp = ybase + (size_t)vec * H;
 
@@ -143,6 +148,7 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
 #pragma unroll 4
                 for (int g = lane; g < G; g += 32) {
                     Pack4<T> x = ld4<T>(h_s + 4 * g);
+                    if (ADD) add4<T>(x, ld4<T>(a_s + 4 * g));
                     inj.apply(x, ld4<T>(v_s + 4 * g));
                     st4<T>(hp + 4 * g, x);   // h' to HBM
                     st4<T>(h_s + 4 * g, x);  // and kept for the second pass
@@ -162,6 +168,7 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
                         const int g = g0 + 32 * u;
                         if (g < G) {
                             Pack4<T> x = ld4<T>(h_s + 4 * g);
+                            if (ADD) add4<T>(x, ld4<T>(a_s + 4 * g));
                             inj.apply(x, vv[u]);
                             st4<T>(hp + 4 * g, x);
                             st4<T>(h_s + 4 * g, x);
@@ -169,6 +176,15 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
                         }
                     }
                 }
+            }
+        } else if (ADD) {
+#pragma unroll 4
+            for (int g = lane; g < G; g += 32) {
+                Pack4<T> x = ld4<T>(h_s + 4 * g);
+                add4<T>(x, ld4<T>(a_s + 4 * g));
+                st4<T>(hp + 4 * g, x);
+                st4<T>(h_s + 4 * g, x);
+                sumsq4<T>(x, a0, a1, a2, a3);
             }
         } else {
 #pragma unroll 4
@@ -189,10 +205,10 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     }
 }
 
-template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V> static int launch_tma(const K2Params &p, cudaStream_t s) {
+template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, bool ADD> static int launch_tma(const K2Params &p, cudaStream_t s) {
     const size_t row_bytes = (size_t)p.H * sizeof(T);
     const size_t budget = 220 * 1024;
-    constexpr int kRowsPerStage = STAGE_V ? 2 : 1;
+    constexpr int kRowsPerStage = 1 + (ADD ? 1 : 0) + (STAGE_V ? 1 : 0);
     if (row_bytes + 1024 + kRowsPerStage * S * row_bytes > budget) return IA_ERR_TOO_LARGE;
     int nwarps = (int)((budget - row_bytes - 1024) / (kRowsPerStage * S * row_bytes));
     if (nwarps > 16) nwarps = 16;
@@ -202,7 +218,7 @@ template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V> static int la
     if (nwarps > per_sm) nwarps = per_sm < 1 ? 1 : per_sm;
     const size_t bars_off = (row_bytes + 127) & ~(size_t)127;
     const size_t smem = bars_off + (((size_t)nwarps * S * 8 + 127) & ~(size_t)127) + (size_t)nwarps * kRowsPerStage * S * row_bytes;
-    auto kern = k2_tma_kernel<T, VARIANT, IEEE, S, STAGE_V>;
+    auto kern = k2_tma_kernel<T, VARIANT, IEEE, S, STAGE_V, ADD>;
     // opt in to large dynamic shared memory once per instantiation and device (first call = a warm-up
     // call, i.e. not under stream capture)
     static bool configured[64] = {false};
@@ -220,19 +236,24 @@ template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V> static int la
     return (int)cudaGetLastError();
 }
 
-template <typename T, int S, bool STAGE_V> static int tma_flags_s(const K2Params &p, int variant, int flags, cudaStream_t s) {
+template <typename T, int S, bool STAGE_V, bool ADD> static int tma_flags_s(const K2Params &p, int variant, int flags, cudaStream_t s) {
     const bool ieee = (flags & IA_RSQRT_IEEE) != 0;
     if (variant == IA_NORM_GEMMA)
-        return ieee ? launch_tma<T, IA_NORM_GEMMA, true, S, STAGE_V>(p, s) : launch_tma<T, IA_NORM_GEMMA, false, S, STAGE_V>(p, s);
-    return ieee ? launch_tma<T, IA_NORM_LLAMA, true, S, STAGE_V>(p, s) : launch_tma<T, IA_NORM_LLAMA, false, S, STAGE_V>(p, s);
+        return ieee ? launch_tma<T, IA_NORM_GEMMA, true, S, STAGE_V, ADD>(p, s)
+                    : launch_tma<T, IA_NORM_GEMMA, false, S, STAGE_V, ADD>(p, s);
+    return ieee ? launch_tma<T, IA_NORM_LLAMA, true, S, STAGE_V, ADD>(p, s) : launch_tma<T, IA_NORM_LLAMA, false, S, STAGE_V, ADD>(p, s);
 }
 
 template <typename T> static int tma_flags(const K2Params &p, int variant, int flags, cudaStream_t s) {
     // Long launches: table rows come from L2 and a stage holds only the residual row, which doubles the
     // warps per SM (12 at H = 4096) — measured 1.29 vs 1.18 of the copy-bandwidth peak at 262 144 vectors.
     // Short launches are latency-bound: there the table row rides in the stage (10.4 vs 12.9 us at 200).
-    if (p.nvec >= 8192) return tma_flags_s<T, 2, false>(p, variant, flags, s);
-    return tma_flags_s<T, 2, true>(p, variant, flags, s);
+    if (p.add) {
+        // with the branch row staged as well, the table row always comes from L2 (two rows per stage)
+        return tma_flags_s<T, 2, false, true>(p, variant, flags, s);
+    }
+    if (p.nvec >= 8192) return tma_flags_s<T, 2, false, false>(p, variant, flags, s);
+    return tma_flags_s<T, 2, true, false>(p, variant, flags, s);
 }
 
 int launch_k2_tma(const K2Params &p, int dtype, int vec_dtype, int variant, int flags, cudaStream_t s) {

@@ -10,6 +10,7 @@ struct K2Params {
     void *h;            // [nvec, H] in/out (TAIL: residual in/out)
     void *y;            // [nvec, H] out
     const void *mlp;    // TAIL only: [nvec, H] MLP output
+    const void *add;    // optional [nvec, H]: branch output added to h first (h = rd(h + add)), else NULL
     const void *vtable; // [n_vec, H]
     const int32_t *row_vec;
     const float *row_alpha;
@@ -96,6 +97,16 @@ template <typename T, typename VT> struct Injector {
     }
 };
 
+// x group = round(x group + a group): the decoder layer's `residual + branch_output`.
+template <typename T> __device__ __forceinline__ void add4(Pack4<T> &x, const Pack4<T> &a) {
+    float f[4], af[4];
+    Elt<T>::unpack(x, f);
+    Elt<T>::unpack(a, af);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) f[i] = __fadd_rn(f[i], af[i]);
+    Elt<T>::rd4(f, x);
+}
+
 // ---- bf16 fast paths: two elements per instruction, same bits -----------------------------------
 // torch computes a bf16 op as: widen to fp32, one fp32 op (rounded), round to bf16.  For bf16
 // operands that double rounding is provably the single rounding `mul.rn.bf16x2` / `add.rn.bf16x2`
@@ -124,6 +135,11 @@ template <> struct Injector<__nv_bfloat16, __nv_bfloat16> {
         x.raw.y = as_u32(__hadd2_rn(as_bf162(x.raw.y), s1));
     }
 };
+
+template <> __device__ __forceinline__ void add4<__nv_bfloat16>(Pack4<__nv_bfloat16> &x, const Pack4<__nv_bfloat16> &a) {
+    x.raw.x = as_u32(__hadd2_rn(as_bf162(x.raw.x), as_bf162(a.raw.x)));
+    x.raw.y = as_u32(__hadd2_rn(as_bf162(x.raw.y), as_bf162(a.raw.y)));
+}
 
 template <>
 __device__ __forceinline__ void norm4<__nv_bfloat16, IA_NORM_LLAMA>(const Pack4<__nv_bfloat16> &x, float r,

@@ -103,6 +103,77 @@ static int launch_rope(const void *q, const void *k, const void *c, const void *
     return (int)cudaGetLastError();
 }
 
+
+// Rotary embedding of q and k plus the KV-cache append, one launch: q goes to a dense
+// [tokens, n_heads, D] buffer, rotated k and the untouched v go straight to their cache slots
+// dst[b][head][pos0 + t][:] (element strides sb / sh / sp), b = token / T, t = token % T.  Same
+// arithmetic as rope_kernel; what disappears is the separate rotated-k tensor and the two strided
+// copies that moved k and v into the cache.  Inputs may be slices of one fused projection output:
+// each has its own token-row stride.
+struct RopeAppend {
+    const void *q, *k, *v;
+    long q_rs, k_rs, v_rs;  // elements between consecutive tokens
+    const void *cosv, *sinv;
+    void *q_out, *k_dst, *v_dst;
+    long sb, sh, sp;
+    long tokens;
+    int T, pos0, nh, nkv, D;
+};
+
+template <typename T> __device__ __forceinline__ void copy8x2(const T *x, int half, T *o) {
+    if (sizeof(T) == 2) {
+        *reinterpret_cast<uint4 *>(o) = *reinterpret_cast<const uint4 *>(x);
+        *reinterpret_cast<uint4 *>(o + half) = *reinterpret_cast<const uint4 *>(x + half);
+    } else {
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            *reinterpret_cast<uint4 *>(o + 4 * q) = *reinterpret_cast<const uint4 *>(x + 4 * q);
+            *reinterpret_cast<uint4 *>(o + half + 4 * q) = *reinterpret_cast<const uint4 *>(x + half + 4 * q);
+        }
+    }
+}
+
+template <typename T> __global__ void __launch_bounds__(256) rope_append_kernel(const RopeAppend a) {
+    const int half = a.D >> 1;
+    const int chunks = half >> 3;
+    const int heads = a.nh + 2 * a.nkv;
+    const long total = a.tokens * heads * chunks;
+    const T *cosv = static_cast<const T *>(a.cosv), *sinv = static_cast<const T *>(a.sinv);
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int ch = (int)(i % chunks);
+        const long r = i / chunks;
+        const int head = (int)(r % heads);
+        const long tok = r / heads;
+        const T *c = cosv + tok * a.D + ch * 8;
+        const T *s = sinv + tok * a.D + ch * 8;
+        if (head < a.nh) {
+            const T *src = static_cast<const T *>(a.q) + tok * a.q_rs + (long)head * a.D + ch * 8;
+            Rope8<T>::run(src, c, s, half, static_cast<T *>(a.q_out) + (tok * a.nh + head) * (long)a.D + ch * 8);
+        } else {
+            const long b = tok / a.T;
+            const long t = tok - b * a.T;
+            const bool is_k = head < a.nh + a.nkv;
+            const int hh = head - a.nh - (is_k ? 0 : a.nkv);
+            const long off = b * a.sb + hh * a.sh + (a.pos0 + t) * a.sp + ch * 8;
+            if (is_k)
+                Rope8<T>::run(static_cast<const T *>(a.k) + tok * a.k_rs + (long)hh * a.D + ch * 8, c, s, half,
+                              static_cast<T *>(a.k_dst) + off);
+            else
+                copy8x2<T>(static_cast<const T *>(a.v) + tok * a.v_rs + (long)hh * a.D + ch * 8, half,
+                           static_cast<T *>(a.v_dst) + off);
+        }
+    }
+}
+
+template <typename T> static int launch_rope_append(const RopeAppend &a, cudaStream_t st) {
+    const long total = a.tokens * (a.nh + 2 * a.nkv) * (a.D >> 4);
+    long blocks = (total + 255) / 256;
+    if (blocks > 148L * 16) blocks = 148L * 16;
+    if (blocks < 1) blocks = 1;
+    rope_append_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(a);
+    return (int)cudaGetLastError();
+}
+
 }  // namespace ia
 
 extern "C" int ia_rope(const void *q, const void *k, const void *cosv, const void *sinv, void *q_out, void *k_out,
@@ -118,6 +189,41 @@ extern "C" int ia_rope(const void *q, const void *k, const void *cosv, const voi
     case IA_BF16: return launch_rope<__nv_bfloat16>(q, k, cosv, sinv, q_out, k_out, tokens, (int)n_heads, (int)n_kv_heads, (int)head_dim, st);
     case IA_F16: return launch_rope<__half>(q, k, cosv, sinv, q_out, k_out, tokens, (int)n_heads, (int)n_kv_heads, (int)head_dim, st);
     case IA_F32: return launch_rope<float>(q, k, cosv, sinv, q_out, k_out, tokens, (int)n_heads, (int)n_kv_heads, (int)head_dim, st);
+    default: return IA_ERR_DTYPE;
+    }
+}
+
+extern "C" int ia_rope_append(const void *q, const void *k, const void *v, int64_t q_row_stride, int64_t k_row_stride,
+                              int64_t v_row_stride, const void *cosv, const void *sinv, void *q_out, void *k_dst, void *v_dst,
+                              int64_t dst_batch_stride, int64_t dst_head_stride, int64_t dst_pos_stride, int64_t tokens,
+                              int64_t tokens_per_row, int64_t pos0, int64_t n_heads, int64_t n_kv_heads, int64_t head_dim,
+                              int32_t dtype, void *stream) {
+    using namespace ia;
+    if (!q || !k || !v || !cosv || !sinv || !q_out || !k_dst || !v_dst) return IA_ERR_NULL;
+    if (tokens < 0 || tokens_per_row < 1 || pos0 < 0 || n_heads < 1 || n_kv_heads < 1 || head_dim < 16 || (head_dim & 15) ||
+        head_dim > 1024)
+        return IA_ERR_SHAPE;
+    if (tokens % tokens_per_row) return IA_ERR_SHAPE;
+    const int64_t vec = dtype == IA_F32 ? 4 : 8;  // elements per 16 bytes: every stride keeps 16-byte alignment
+    if (q_row_stride < n_heads * head_dim || k_row_stride < n_kv_heads * head_dim || v_row_stride < n_kv_heads * head_dim)
+        return IA_ERR_SHAPE;
+    if (q_row_stride % vec || k_row_stride % vec || v_row_stride % vec || dst_batch_stride % vec || dst_head_stride % vec ||
+        dst_pos_stride % vec || dst_pos_stride < head_dim)
+        return IA_ERR_ALIGN;
+    if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(cosv) || !aligned16(sinv) || !aligned16(q_out) ||
+        !aligned16(k_dst) || !aligned16(v_dst))
+        return IA_ERR_ALIGN;
+    if (tokens == 0) return 0;
+    RopeAppend a;
+    a.q = q; a.k = k; a.v = v; a.q_rs = q_row_stride; a.k_rs = k_row_stride; a.v_rs = v_row_stride;
+    a.cosv = cosv; a.sinv = sinv; a.q_out = q_out; a.k_dst = k_dst; a.v_dst = v_dst;
+    a.sb = dst_batch_stride; a.sh = dst_head_stride; a.sp = dst_pos_stride; a.tokens = tokens;
+    a.T = (int)tokens_per_row; a.pos0 = (int)pos0; a.nh = (int)n_heads; a.nkv = (int)n_kv_heads; a.D = (int)head_dim;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (dtype) {
+    case IA_BF16: return launch_rope_append<__nv_bfloat16>(a, st);
+    case IA_F16: return launch_rope_append<__half>(a, st);
+    case IA_F32: return launch_rope_append<float>(a, st);
     default: return IA_ERR_DTYPE;
     }
 }

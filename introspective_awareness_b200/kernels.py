@@ -46,9 +46,11 @@ def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: s
                    vtable: Optional[torch.Tensor] = None, row_vec: Optional[torch.Tensor] = None,
                    row_alpha: Optional[torch.Tensor] = None, row_t0: Optional[torch.Tensor] = None,
                    pos0: int = 0, steer_all: bool = False, out: Optional[torch.Tensor] = None,
-                   ieee_rsqrt: bool = False, impl: str = "auto") -> torch.Tensor:
+                   ieee_rsqrt: bool = False, impl: str = "auto", add: Optional[torch.Tensor] = None) -> torch.Tensor:
     """K2.  `h` [rows, T, H] is updated in place with the per-row injection; returns y = RMSNorm(h').
-    With row_vec None this is a plain RMSNorm of `variant`.  impl: "auto" | "regs" | "tma"."""
+    With row_vec None this is a plain RMSNorm of `variant`.  impl: "auto" | "regs" | "tma".
+    add: a branch output [rows, T, H] that is added to h first (h <- h + add, rounded), the decoder
+    layer's residual add folded into the same pass; h is then rewritten for every vector."""
     if h.dim() != 3:
         raise ValueError("h must be [rows, T, H]")
     rows, t_len, hid = h.shape
@@ -56,6 +58,16 @@ def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: s
     flags = ((IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
              | {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS}[impl])
     lib = _lib.load()
+    if add is not None:
+        if add.shape != h.shape:
+            raise ValueError("add must have the shape of h")
+        rc = lib.ia_add_inject_rmsnorm(
+            _cuda(h, "h"), _cuda(add, "add", h.dtype), _cuda(y, "out", h.dtype), _cuda(vtable, "vtable"),
+            _cuda(row_vec, "row_vec", torch.int32), _cuda(row_alpha, "row_alpha", torch.float32),
+            _cuda(row_t0, "row_t0", torch.int32), _cuda(weight, "weight", h.dtype), float(eps), rows, t_len, hid, int(pos0),
+            _dt(h), _dt(vtable) if vtable is not None else _dt(h), VARIANTS[variant], flags, _stream())
+        check(rc, "ia_add_inject_rmsnorm")
+        return y
     rc = lib.ia_inject_rmsnorm(
         _cuda(h, "h"), _cuda(y, "out", h.dtype), _cuda(vtable, "vtable"), _cuda(row_vec, "row_vec", torch.int32),
         _cuda(row_alpha, "row_alpha", torch.float32), _cuda(row_t0, "row_t0", torch.int32),
@@ -227,3 +239,55 @@ def rope(q: torch.Tensor, k: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor)
                              b * t, nh, nkv, d, _dt(q), _stream())
     check(rc, "ia_rope")
     return qo, ko
+
+
+def _rows_view(t: torch.Tensor, width: int, name: str) -> Tuple[int, int]:
+    """(pointer, row stride in elements) of a [..., width] tensor whose leading dims collapse to rows with
+    one stride — a dense tensor or a column slice of one (e.g. part of a fused projection output)."""
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if t.shape[-1] != width or t.stride(-1) != 1:
+        raise ValueError(f"{name}: last dim must be {width} and dense")
+    rs = t.stride(-2) if t.dim() >= 2 else width
+    for d in range(t.dim() - 2):
+        if t.shape[d] != 1 and t.stride(d) != t.stride(d + 1) * t.shape[d + 1]:
+            raise ValueError(f"{name}: rows do not have a single stride")
+    return t.data_ptr(), rs
+
+
+def rope_append(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor,
+                k_dst: torch.Tensor, v_dst: torch.Tensor, pos0: int, n_heads: int, n_kv: int, head_dim: int) -> torch.Tensor:
+    """Rotary embedding of q and k and the KV append in one launch.  q [B, T, n_heads*D], k / v
+    [B, T, n_kv*D] (dense, or column slices of one fused projection output); cos / sin [B, T, D] dense;
+    k_dst / v_dst [B, n_kv, L, D] (any batch/head/position strides, D dense): positions pos0 .. pos0+T-1
+    are written.  Returns rotated q as a [B, n_heads, T, D] view of a dense [B, T, n_heads, D] tensor."""
+    b, t = q.shape[0], q.shape[1]
+    qp, qrs = _rows_view(q, n_heads * head_dim, "q")
+    kp, krs = _rows_view(k, n_kv * head_dim, "k")
+    vp, vrs = _rows_view(v, n_kv * head_dim, "v")
+    if tuple(cos.shape) != (b, t, head_dim) or tuple(sin.shape) != (b, t, head_dim):
+        raise ValueError("cos/sin must be [B, T, D]")
+    if k_dst.shape != v_dst.shape or k_dst.stride() != v_dst.stride() or k_dst.stride(3) != 1:
+        raise ValueError("k_dst / v_dst must share a layout with a dense head dimension")
+    if k_dst.shape[0] != b or k_dst.shape[1] != n_kv or k_dst.shape[3] != head_dim or pos0 + t > k_dst.shape[2]:
+        raise ValueError("destination does not fit")
+    q_out = torch.empty((b, t, n_heads, head_dim), dtype=q.dtype, device=q.device)
+    rc = _lib.load().ia_rope_append(qp, kp, vp, qrs, krs, vrs, _cuda(cos, "cos", q.dtype), _cuda(sin, "sin", q.dtype),
+                                    q_out.data_ptr(), k_dst.data_ptr(), v_dst.data_ptr(), k_dst.stride(0), k_dst.stride(1),
+                                    k_dst.stride(2), b * t, t, int(pos0), n_heads, n_kv, head_dim, _dt(q), _stream())
+    check(rc, "ia_rope_append")
+    return q_out.transpose(1, 2)
+
+
+def silu_mul(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
+    """round(round(silu(gate)) * up) in one pass; gate / up [..., I] dense or column slices of one tensor."""
+    width = gate.shape[-1]
+    gp, grs = _rows_view(gate, width, "gate")
+    up_p, urs = _rows_view(up, width, "up")
+    if up.shape != gate.shape or up.dtype != gate.dtype:
+        raise ValueError("gate and up must match")
+    out = torch.empty(gate.shape, dtype=gate.dtype, device=gate.device)
+    rows = out.numel() // width
+    rc = _lib.load().ia_silu_mul(gp, up_p, out.data_ptr(), rows, width, grs, urs, _dt(gate), _stream())
+    check(rc, "ia_silu_mul")
+    return out

@@ -266,8 +266,9 @@ def test_sweep_driver_end_to_end(tmp_path):
 @pytest.mark.parametrize("arch", ["tiny-llama", "tiny-gemma2", "llama-8b-4layer"])
 def test_runtime_optimisations_do_not_change_bits(arch):
     """K2 for every RMSNorm, the fused rotary kernel, the Gemma-2 tail variant, grouped-query SDPA, the
-    CUDA graphs and both K2 implementations, each switched off in turn: same logits, bit for bit (Gemma-2's
-    head_dim 256 grouped-query path excepted, see above)."""
+    CUDA graphs, the once-per-forward mask conversion, the engine-driven Llama block (residual add inside K2,
+    rotary + KV append, SiLU-gate multiply) and the single-GEMM q/k/v and gate/up projections, each switched
+    off in turn: same logits, bit for bit (Gemma-2's head_dim 256 grouped-query path excepted, see above)."""
     from introspective_awareness_b200.synthetic import synthetic_prompt_ids
 
     w = _wrapper(arch, torch.bfloat16, 9 if arch.startswith("tiny") else None, attention="hf")
@@ -286,7 +287,9 @@ def test_runtime_optimisations_do_not_change_bits(arch):
         return out, torch.stack(w.last_session.step_logits).cpu()
 
     base_ids, base_logits = run()
-    settings = [("fused_norms", False), ("fused_rope", False), ("graph_decode", False)]
+    settings = [("fused_norms", False), ("fused_rope", False), ("graph_decode", False), ("additive_masks", False)]
+    if eng.native_block:  # Llama / Qwen2: the block driven by the engine vs the HF layer forwards
+        settings += [("native_block", False), ("fuse_projections", False)]
     if eng.is_gemma2:
         settings.append(("fuse_gemma_tail", False))
     else:

@@ -282,3 +282,73 @@ def test_full_size_properties():
     y3 = kernels.inject_rmsnorm(h3, w, 1e-5, "llama", vtable=vt, row_vec=row_vec[perm].contiguous(),
                                 row_alpha=alpha[perm].contiguous(), row_t0=t0[perm].contiguous())
     assert torch.equal(h3, h1[perm]) and torch.equal(y3, y1[perm])
+
+
+@pytest.mark.parametrize("dt", ["bf16", "f16", "f32"])
+@pytest.mark.parametrize("variant", ["llama", "gemma"])
+def test_residual_add_form_bit_exact_against_oracle(dt, variant):
+    """ia_add_inject_rmsnorm: h <- rd(h + add) first (the decoder layer's residual add), then K2 as
+    before.  Oracle = the same numpy K2 applied to rd(h + add).  Covers the bulk-copy kernel (H % 128 == 0),
+    the two-pass kernel (other H, fp32 table) and un-steered launches, where h must still be rewritten."""
+    from introspective_awareness_b200 import kernels
+
+    dev = _dev()
+    shapes = [(5, 3, 128), (4, 9, 896), (4, 3, 3584), (9, 2, 4096), (3, 3, 5120), (700, 3, 256), (1, 1, 132), (3, 2, 1000)]
+    for k, (rows, T, H) in enumerate(shapes):
+        if dt == "f32" and H > 4096:
+            continue
+        h, vt, vt_m, w, row_vec, alpha, t0 = make_inputs(rows, T, H, dt, 900 + k, gemma=variant == "gemma")
+        add = K.rd(np.random.default_rng(77 + k).standard_normal((rows, T, H)).astype(np.float32) * 0.7, dt)
+        summed = K.rd(h + add, dt)
+        eps = 1e-5 if variant == "llama" else 1e-6
+        for steer_all, pos0, steered in ((False, 0, True), (True, 3, True), (False, 0, False)):
+            if steered:
+                want_h, want_y = K.inject_rmsnorm(summed, vt_m, row_vec, alpha, t0, pos0, steer_all, w, eps, variant, dt)
+            else:
+                want_h = summed
+                want_y = K.rmsnorm(summed.reshape(rows * T, H), w, eps, variant, dt).reshape(rows, T, H)
+            for vec_f32 in ((False, True) if dt == "bf16" and steered else (False,)):
+                h_t, add_t = to_model(h, dt, dev), to_model(add, dt, dev)
+                kw = {}
+                if steered:
+                    kw = dict(vtable=torch.from_numpy(vt_m).to(dev) if vec_f32 else to_model(vt_m, dt, dev),
+                              row_vec=torch.from_numpy(row_vec).to(dev), row_alpha=torch.from_numpy(alpha).to(dev),
+                              row_t0=torch.from_numpy(t0).to(dev), pos0=pos0, steer_all=steer_all)
+                y = kernels.inject_rmsnorm(h_t, to_model(w, dt, dev), eps, variant, ieee_rsqrt=True, add=add_t, **kw)
+                torch.cuda.synchronize()
+                assert np.array_equal(h_t.float().cpu().numpy(), want_h), (dt, variant, rows, T, H, steer_all, steered, vec_f32)
+                assert np.array_equal(y.float().cpu().numpy(), want_y), (dt, variant, rows, T, H, steer_all, steered, vec_f32)
+                assert torch.equal(add_t, to_model(add, dt, dev))  # the branch output is only read
+
+
+@pytest.mark.parametrize("H,rows,T", [(4096, 200, 1), (4096, 64, 128), (896, 16, 37), (5120, 200, 1)])
+def test_residual_add_form_bit_identical_to_eager_torch(H, rows, T):
+    """Default flags (hardware rsqrt): residual + branch -> hook add -> LlamaRMSNorm, eager on the same GPU."""
+    from transformers.models.llama.modeling_llama import LlamaRMSNorm
+
+    from introspective_awareness_b200 import kernels
+
+    dev = _dev()
+    g = torch.Generator(device=dev).manual_seed(H + rows)
+    resid = torch.randn(rows, T, H, device=dev, generator=g).to(torch.bfloat16)
+    branch = (torch.randn(rows, T, H, device=dev, generator=g) * 0.5).to(torch.bfloat16)
+    table = (torch.randn(5, H, device=dev, generator=g) * 0.3).to(torch.bfloat16)
+    row_vec = torch.arange(rows, device=dev, dtype=torch.int32) % 6 - 1
+    alpha = torch.tensor([1.0, 2.0, 4.0, 8.0], device=dev)[torch.arange(rows, device=dev) % 4].float()
+    t0 = (torch.arange(rows, device=dev, dtype=torch.int32) * 7) % (T + 1)
+    norm = LlamaRMSNorm(H, 1e-5).to(dev).to(torch.bfloat16)
+    with torch.no_grad():
+        norm.weight.copy_((torch.randn(H, device=dev, generator=g) * 0.02 + 1).to(torch.bfloat16))
+        want_h = resid + branch
+        for b in range(rows):
+            if int(row_vec[b]) >= 0:
+                sv = table[int(row_vec[b])] * alpha[b].to(torch.bfloat16)  # the reference scales in the model dtype
+                want_h[b, int(t0[b]):] = want_h[b, int(t0[b]):] + sv
+        want_y = norm(want_h)
+    # alpha values above are exactly representable in bf16, as the reference's strengths are
+    h = resid.clone()
+    y = kernels.inject_rmsnorm(h, norm.weight.data, 1e-5, "llama", vtable=table, row_vec=row_vec, row_alpha=alpha,
+                               row_t0=t0, pos0=0, add=branch)
+    torch.cuda.synchronize()
+    assert torch.equal(h, want_h)
+    assert torch.equal(y, want_y)

@@ -68,3 +68,68 @@ def test_graph_capture_survives_a_garbage_collection_of_older_sessions(monkeypat
         assert first.shape == (4, 6) and second.shape == (6, 6)
     finally:
         gc.set_threshold(*old)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("B,T,nh,nkv,D,pos0,fused", [(200, 1, 32, 8, 128, 140, True), (3, 37, 14, 2, 64, 0, False),
+                                                     (2, 16, 16, 8, 256, 5, True), (5, 1, 4, 4, 32, 0, False)])
+def test_rope_append_matches_hf_rotary_plus_cache_update(dtype, B, T, nh, nkv, D, pos0, fused):
+    """One launch = apply_rotary_pos_emb + the two copies of `past_key_values.update`, bit for bit; inputs
+    either three dense projections or column slices of one fused projection output."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from transformers.models.llama.modeling_llama import apply_rotary_pos_emb
+
+    from introspective_awareness_b200 import kernels
+
+    dev = "cuda:0"
+    g = torch.Generator(device=dev).manual_seed(B * 100 + T)
+    n = (nh + 2 * nkv) * D
+    qkv = torch.randn(B, T, n, device=dev, generator=g).to(dtype)
+    q, k, v = qkv.split([nh * D, nkv * D, nkv * D], dim=-1)
+    if not fused:
+        q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+    ang = torch.rand(B, T, D // 2, device=dev, generator=g) * 6.28
+    emb = torch.cat((ang, ang), dim=-1)
+    cos, sin = emb.cos().to(dtype), emb.sin().to(dtype)
+    L = pos0 + T + 3
+    kc = torch.full((B, nkv, L, D), 7.0, device=dev, dtype=dtype)
+    vc = torch.full((B, nkv, L, D), 7.0, device=dev, dtype=dtype)
+    want_q, want_k = apply_rotary_pos_emb(q.reshape(B, T, nh, D).transpose(1, 2), k.reshape(B, T, nkv, D).transpose(1, 2), cos, sin)
+    want_kc, want_vc = kc.clone(), vc.clone()
+    want_kc[:, :, pos0:pos0 + T] = want_k
+    want_vc[:, :, pos0:pos0 + T] = v.reshape(B, T, nkv, D).transpose(1, 2)
+    got_q = kernels.rope_append(q, k, v, cos, sin, kc, vc, pos0, nh, nkv, D)
+    torch.cuda.synchronize()
+    assert got_q.shape == want_q.shape and torch.equal(got_q, want_q)
+    assert torch.equal(kc, want_kc) and torch.equal(vc, want_vc)   # slot written, everything else untouched
+    # cache-less form: destination is a transposed view of a dense [B, T, n_kv, D] buffer
+    kd = torch.empty(B, T, nkv, D, device=dev, dtype=dtype).transpose(1, 2)
+    vd = torch.empty(B, T, nkv, D, device=dev, dtype=dtype).transpose(1, 2)
+    kernels.rope_append(q, k, v, cos, sin, kd, vd, 0, nh, nkv, D)
+    assert torch.equal(kd, want_k) and torch.equal(vd, v.reshape(B, T, nkv, D).transpose(1, 2))
+    with pytest.raises(ValueError):
+        kernels.rope_append(q, k, v, cos, sin, kc, vc, L - T + 1, nh, nkv, D)   # would run past the cache
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("rows,width,fused", [(200, 14336, True), (7, 4864, False), (3, 256, True), (25600, 1024, False)])
+def test_silu_mul_is_bit_identical_to_the_two_eager_kernels(dtype, rows, width, fused):
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from introspective_awareness_b200 import kernels
+
+    dev = "cuda:0"
+    g = torch.Generator(device=dev).manual_seed(rows + width)
+    gu = (torch.randn(rows, 2 * width, device=dev, generator=g) * 4).to(dtype)
+    gu[0, :8] = torch.tensor([0.0, -0.0, 30.0, -30.0, 88.0, -88.0, 1e-3, -1e-3], device=dev).to(dtype)  # tails of exp
+    gate, up = gu.split(width, dim=-1)
+    if not fused:
+        gate, up = gate.contiguous(), up.contiguous()
+    want = torch.nn.functional.silu(gate) * up
+    got = kernels.silu_mul(gate, up)
+    torch.cuda.synchronize()
+    assert got.is_contiguous() and torch.equal(got, want)
+    got3 = kernels.silu_mul(gate.reshape(1, rows, width) if not fused else gate.unflatten(0, (1, rows)),
+                            up.reshape(1, rows, width) if not fused else up.unflatten(0, (1, rows)))
+    assert torch.equal(got3[0], want)
