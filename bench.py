@@ -259,13 +259,15 @@ def run_ours(args):
     k2_ms = [a.elapsed_time(b) for a, b, _ in k2_events]
     H = eng.hidden
     tail = eng.fuse_gemma_tail  # Gemma-2: the block-tail variant reads mlp_out as a fifth stream and a second weight
-    algo = rows * T_PROMPT * H * 2 * (5 if tail else 4) + H * 2 * (2 if tail else 1)
+    # Llama / Qwen2 (engine-driven block): the launch is the residual-add form — the MLP output is a fifth stream
+    fifth = tail or eng.native_block
+    algo = rows * T_PROMPT * H * 2 * (5 if fifth else 4) + H * 2 * (2 if tail else 1)
     peak, peak_src = peak_hbm()
     k2_avg_ms = sum(k2_ms) / max(len(k2_ms), 1)
     achieved = algo / (k2_avg_ms * 1e6) if k2_ms else None
     # what this particular launch actually moves: only positions >= t0 read a table row and write h'
     steered_vecs = int((T_PROMPT - t0_abs.clamp(max=T_PROMPT)).sum())
-    moved = (rows * T_PROMPT * (4 if tail else 2) + steered_vecs * (1 if tail else 2)) * H * 2 + H * 2
+    moved = (rows * T_PROMPT * (4 if fifth else 2) + steered_vecs * (1 if fifth else 2)) * H * 2 + H * 2
 
     h2d = sum(t.numel() * t.element_size() for t in (h_c_ids, h_c_mask, h_b_ids, h_b_mask, h_ids, h_mask)) \
         + N_CONCEPTS * H * 2 + rows * (4 + 4 + 4)
@@ -291,13 +293,18 @@ def run_ours(args):
                             f"layer, one {rows}-row steered batch per GPU, prompt {T_PROMPT} (real {T_MIN}..{T_PROMPT}, "
                             f"left-padded), {N_NEW} greedy tokens, extraction {N_CONCEPTS}+{N_BASE} prompts per step",
                 "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": eng.attention,
+                "engine_block": "native" if eng.native_block else "hf",
+                "single_gemm_projections": {f"{k}{list(shape)}": ok for (k, shape), ok in sorted(eng._fused_checked.items())},
                 "parallelism": "independent replicas, layer axis round-robin" if world > 1 else "single replica",
                 "l2": "inputs larger than L2: each step streams 16 GB of weights per decode step and ~1 GB of KV/activations",
             },
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "gpu_launches_by_kernel": launches_by_kernel,
-            "roofline": {"kernel": "ia_inject_rmsnorm (ia::k2_tma_kernel: fused inject+RMSNorm, cp.async.bulk staged), prompt-pass launch", "bound": "hbm",
+            "roofline": {"kernel": ("ia_add_inject_rmsnorm (ia::k2_tma_kernel, ADD form: residual add + inject + RMSNorm, cp.async.bulk "
+                                    "staged), prompt-pass launch" if eng.native_block else
+                                    "ia_inject_rmsnorm (ia::k2_tma_kernel: fused inject+RMSNorm, cp.async.bulk staged), prompt-pass launch"),
+                         "bound": "hbm",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
                          "traffic": traffic_from_profiles(), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo, "us_per_launch": k2_avg_ms * 1e3,
@@ -306,13 +313,16 @@ def run_ours(args):
                          "frac_of_peak_on_bytes_moved": (moved / (k2_avg_ms * 1e6) / peak) if k2_ms else None,
                          "launches_timed": len(k2_ms),
                          "share_of_step": (k2_avg_ms * len(k2_ms) / ms_res) if k2_ms else None,
-                         "note": "achieved uses SURVEY 8(d)'s algorithmic bytes (4 streams for every vector). In this "
-                                 "launch only positions >= t0 (steered_fraction_of_vectors) read a table row and write h', "
-                                 "so fewer bytes actually move (bytes_moved_per_launch, frac_of_peak_on_bytes_moved); the "
-                                 "input residual was also just written by the preceding kernel (partly L2-resident). The "
-                                 "cold-cache, every-vector-steered figure for the same shape is 1.10 of peak on algorithmic "
-                                 "bytes / 0.77 on DRAM bytes (profiles/k2_prefill_ncu_summary.json, whose DRAM byte count is "
-                                 "`traffic`; tools/kbench.py)"},
+                         "streams_per_vector": 5 if fifth else 4,
+                         "note": "achieved uses SURVEY 8(d)'s algorithmic bytes: residual in, table row in, h' out, y out for "
+                                 "every vector, plus the branch output in when the layer's residual add is folded into the "
+                                 "launch (streams_per_vector). In this launch only positions >= t0 "
+                                 "(steered_fraction_of_vectors) read a table row, so fewer bytes actually move "
+                                 "(bytes_moved_per_launch, frac_of_peak_on_bytes_moved); the branch output was also just "
+                                 "written by the preceding GEMM (partly L2-resident). Cold-cache, every-vector-steered "
+                                 "figures for the same shape: tools/kbench.py -> profiles/r1_kbench_ladder.jsonl; `traffic` "
+                                 "is the DRAM byte count of the 4-stream kernel's ncu capture "
+                                 "(profiles/k2_prefill_ncu_summary.json)"},
             "cpu_baseline": cpu,
             "clocks": clocks,
         }

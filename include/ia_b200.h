@@ -50,6 +50,7 @@ extern "C" {
 #define IA_RSQRT_IEEE 2  /* r = 1/sqrt(.) with IEEE div+sqrt (torch CPU) instead of rsqrtf (torch CUDA) */
 #define IA_IMPL_TMA 4    /* force the bulk-copy (TMA, cp.async.bulk + mbarrier) staged implementation */
 #define IA_IMPL_REGS 8   /* force the register-resident implementation */
+#define IA_IMPL_ADD_STAGED 16 /* ia_add_inject_rmsnorm: bulk-copy the branch row into the stage even in long launches */
 /* neither bit: automatic — TMA staging when a row is >= 4 KiB and the table is in the model dtype */
 
 /* extraction methods (ia_gather_meandiff / ia_meandiff_finalize `mode`) */

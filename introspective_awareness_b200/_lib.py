@@ -14,7 +14,7 @@ HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "ia_b200.h")
 
 IA_BF16, IA_F16, IA_F32 = 0, 1, 2
 IA_NORM_LLAMA, IA_NORM_GEMMA = 0, 1
-IA_STEER_ALL, IA_RSQRT_IEEE, IA_IMPL_TMA, IA_IMPL_REGS = 1, 2, 4, 8
+IA_STEER_ALL, IA_RSQRT_IEEE, IA_IMPL_TMA, IA_IMPL_REGS, IA_IMPL_ADD_STAGED = 1, 2, 4, 8, 16
 IA_MODE_BASELINE, IA_MODE_SIMPLE, IA_MODE_RAW, IA_MODE_POSNEG = 0, 1, 2, 3
 
 

@@ -338,9 +338,9 @@ extern "C" int ia_add_inject_rmsnorm(void *h, const void *add, void *y, const vo
     p.h = h; p.y = y; p.mlp = nullptr; p.add = add; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
     p.row_t0 = row_t0; p.w = w; p.w_post = nullptr; p.eps = eps; p.inv_h = 1.0f / (float)H;
     p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
-    // two staged rows per stage and two stages must fit next to the weight row
+    // the weight row and two one-row stages per warp must fit in shared memory
     const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
-    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 5 + 1024 <= 220 * 1024;
+    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 3 + 1024 <= 220 * 1024;
     if (flags & IA_IMPL_TMA) {
         if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
     }

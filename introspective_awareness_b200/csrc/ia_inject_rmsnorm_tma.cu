@@ -66,9 +66,14 @@ template <typename T> __device__ __forceinline__ RowMeta load_meta(const K2Param
 // S = stages per warp: one being consumed, S-1 being filled (prefetch distance S-1 vectors).
 // STAGE_V: the concept-table row is bulk-copied into the stage too (16 KB per stage at H = 4096);
 // otherwise it is read from L2 with batched 64-bit loads and a stage holds only the residual row.
-// ADD: a second [nvec, H] input (the branch output of the decoder layer) is staged next to the
-// residual row and added first, h = rd(h + add); h' is then written for every vector.
-template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, bool ADD>
+// ADD: a second [nvec, H] input (the branch output of the decoder layer) is added first,
+// h = rd(h + add), and h' is then written for every vector.  kAddStaged: the branch row is
+// bulk-copied into the stage next to the residual row (short launches: everything arrives behind one
+// barrier).  kAddLoaded: it comes through registers with batched loads, the stage stays one row and
+// twice as many warps fit (long launches).
+constexpr int kAddNone = 0, kAddStaged = 1, kAddLoaded = 2;
+
+template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, int ADD>
 __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int H = p.H;
@@ -80,7 +85,7 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     const unsigned bars_off = (row_bytes + 127u) & ~127u;
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem + bars_off) + warp * S;
     const unsigned stage_off = bars_off + ((unsigned)(nwarps * S * 8 + 127) & ~127u);
-    constexpr int kRowsPerStage = 1 + (ADD ? 1 : 0) + (STAGE_V ? 1 : 0);
+    constexpr int kRowsPerStage = 1 + (ADD == kAddStaged ? 1 : 0) + (STAGE_V ? 1 : 0);
     unsigned char *my_stage = smem + stage_off + (size_t)warp * S * kRowsPerStage * row_bytes;
 
     for (int g = threadIdx.x; g < G; g += blockDim.x)
@@ -104,10 +109,11 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
             unsigned char *dst = my_stage + (size_t)stage * kRowsPerStage * row_bytes;
             fence_proxy_async();  // earlier generic-proxy accesses to this stage are done (warp synced)
             const bool with_v = STAGE_V && m.steer;
-            mbar_expect_tx(&bars[stage], (1u + (ADD ? 1u : 0u) + (with_v ? 1u : 0u)) * row_bytes);
+            mbar_expect_tx(&bars[stage], (1u + (ADD == kAddStaged ? 1u : 0u) + (with_v ? 1u : 0u)) * row_bytes);
             bulk_g2s(dst, hbase + (size_t)v * H, row_bytes, &bars[stage]);
-            if (ADD) bulk_g2s(dst + row_bytes, abase + (size_t)v * H, row_bytes, &bars[stage]);
-            if (with_v) bulk_g2s(dst + (ADD ? 2 : 1) * row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
+            if (ADD == kAddStaged) bulk_g2s(dst + row_bytes, abase + (size_t)v * H, row_bytes, &bars[stage]);
+            // (an L2 bulk prefetch of the register-loaded branch row here was measured slower: 177 vs 168 us at 25 600 x 4096)
+            if (with_v) bulk_g2s(dst + (ADD == kAddStaged ? 2 : 1) * row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
         }
     };
 
@@ -136,55 +142,55 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
         const int stage = it % S;
         mbar_wait(&bars[stage], (unsigned)(it / S) & 1u);
         T *h_s = reinterpret_cast<T *>(my_stage + (size_t)stage * kRowsPerStage * row_bytes);
-        const T *a_s = reinterpret_cast<const T *>(reinterpret_cast<unsigned char *>(h_s) + row_bytes);  // ADD only
-        const T *v_s = reinterpret_cast<const T *>(reinterpret_cast<unsigned char *>(h_s) + (ADD ? 2 : 1) * row_bytes);
+        const T *a_s = reinterpret_cast<const T *>(reinterpret_cast<unsigned char *>(h_s) + row_bytes);  // kAddStaged only
+        const T *v_s = reinterpret_cast<const T *>(reinterpret_cast<unsigned char *>(h_s) + (ADD == kAddStaged ? 2 : 1) * row_bytes);
         T *hp = hbase + (size_t)vec * H;
         T *yp = ybase + (size_t)vec * H;
+        const Injector<T, T> inj(cur.alpha);
 
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-        if (cur.steer) {
-            const Injector<T, T> inj(cur.alpha);
-            if (STAGE_V) {
-#pragma unroll 4
-                for (int g = lane; g < G; g += 32) {
-                    Pack4<T> x = ld4<T>(h_s + 4 * g);
-                    if (ADD) add4<T>(x, ld4<T>(a_s + 4 * g));
-                    inj.apply(x, ld4<T>(v_s + 4 * g));
-                    st4<T>(hp + 4 * g, x);   // h' to HBM
-                    st4<T>(h_s + 4 * g, x);  // and kept for the second pass
-                    sumsq4<T>(x, a0, a1, a2, a3);
-                }
-            } else {
-                // table row straight from L2, 8 loads in flight per lane (the stores below would
-                // otherwise keep the compiler from hoisting them)
-                const T *vp = vtab + (size_t)cur.vi * H;
-                for (int g0 = lane; g0 < G; g0 += 32 * 8) {
-                    Pack4<T> vv[8];
-#pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (g0 + 32 * u < G) vv[u] = ld4_ro<T>(vp + 4 * (g0 + 32 * u));
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) {
-                        const int g = g0 + 32 * u;
-                        if (g < G) {
-                            Pack4<T> x = ld4<T>(h_s + 4 * g);
-                            if (ADD) add4<T>(x, ld4<T>(a_s + 4 * g));
-                            inj.apply(x, vv[u]);
-                            st4<T>(hp + 4 * g, x);
-                            st4<T>(h_s + 4 * g, x);
-                            sumsq4<T>(x, a0, a1, a2, a3);
-                        }
-                    }
-                }
-            }
-        } else if (ADD) {
+        if (STAGE_V && cur.steer) {
 #pragma unroll 4
             for (int g = lane; g < G; g += 32) {
                 Pack4<T> x = ld4<T>(h_s + 4 * g);
-                add4<T>(x, ld4<T>(a_s + 4 * g));
-                st4<T>(hp + 4 * g, x);
-                st4<T>(h_s + 4 * g, x);
+                if (ADD == kAddStaged) add4<T>(x, ld4<T>(a_s + 4 * g));
+                if (ADD == kAddLoaded) add4<T>(x, ld4_ro<T>(abase + (size_t)vec * H + 4 * g));
+                inj.apply(x, ld4<T>(v_s + 4 * g));
+                st4<T>(hp + 4 * g, x);   // h' to HBM
+                st4<T>(h_s + 4 * g, x);  // and kept for the second pass
                 sumsq4<T>(x, a0, a1, a2, a3);
+            }
+        } else if (cur.steer || ADD != kAddNone) {
+            // operands that are not staged (table row from L2, branch row from HBM when ADD == kAddLoaded) come
+            // through registers, 8 loads each in flight per lane (the stores below would otherwise keep the
+            // compiler from hoisting them)
+            const T *vp = vtab + (size_t)(cur.steer ? cur.vi : 0) * H;
+            const T *ap = abase + (size_t)vec * H;
+            for (int g0 = lane; g0 < G; g0 += 32 * 8) {
+                Pack4<T> vv[8], aa[8];
+                if (ADD == kAddLoaded) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (g0 + 32 * u < G) aa[u] = ld4_ro<T>(ap + 4 * (g0 + 32 * u));
+                }
+                if (cur.steer) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (g0 + 32 * u < G) vv[u] = ld4_ro<T>(vp + 4 * (g0 + 32 * u));
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int g = g0 + 32 * u;
+                    if (g < G) {
+                        Pack4<T> x = ld4<T>(h_s + 4 * g);
+                        if (ADD == kAddStaged) add4<T>(x, ld4<T>(a_s + 4 * g));
+                        if (ADD == kAddLoaded) add4<T>(x, aa[u]);
+                        if (cur.steer) inj.apply(x, vv[u]);
+                        st4<T>(hp + 4 * g, x);
+                        st4<T>(h_s + 4 * g, x);
+                        sumsq4<T>(x, a0, a1, a2, a3);
+                    }
+                }
             }
         } else {
 #pragma unroll 4
@@ -205,10 +211,10 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     }
 }
 
-template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, bool ADD> static int launch_tma(const K2Params &p, cudaStream_t s) {
+template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, int ADD> static int launch_tma(const K2Params &p, cudaStream_t s) {
     const size_t row_bytes = (size_t)p.H * sizeof(T);
     const size_t budget = 220 * 1024;
-    constexpr int kRowsPerStage = 1 + (ADD ? 1 : 0) + (STAGE_V ? 1 : 0);
+    constexpr int kRowsPerStage = 1 + (ADD == kAddStaged ? 1 : 0) + (STAGE_V ? 1 : 0);
     if (row_bytes + 1024 + kRowsPerStage * S * row_bytes > budget) return IA_ERR_TOO_LARGE;
     int nwarps = (int)((budget - row_bytes - 1024) / (kRowsPerStage * S * row_bytes));
     if (nwarps > 16) nwarps = 16;
@@ -236,7 +242,7 @@ template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, bool ADD> sta
     return (int)cudaGetLastError();
 }
 
-template <typename T, int S, bool STAGE_V, bool ADD> static int tma_flags_s(const K2Params &p, int variant, int flags, cudaStream_t s) {
+template <typename T, int S, bool STAGE_V, int ADD> static int tma_flags_s(const K2Params &p, int variant, int flags, cudaStream_t s) {
     const bool ieee = (flags & IA_RSQRT_IEEE) != 0;
     if (variant == IA_NORM_GEMMA)
         return ieee ? launch_tma<T, IA_NORM_GEMMA, true, S, STAGE_V, ADD>(p, s)
@@ -249,11 +255,16 @@ template <typename T> static int tma_flags(const K2Params &p, int variant, int f
     // warps per SM (12 at H = 4096) — measured 1.29 vs 1.18 of the copy-bandwidth peak at 262 144 vectors.
     // Short launches are latency-bound: there the table row rides in the stage (10.4 vs 12.9 us at 200).
     if (p.add) {
-        // with the branch row staged as well, the table row always comes from L2 (two rows per stage)
-        return tma_flags_s<T, 2, false, true>(p, variant, flags, s);
+        // long launches: one-row stages (12 warps at H = 4096), branch and table rows through registers;
+        // short launches: all three rows ride in the stage behind one barrier
+        const size_t rb = (size_t)p.H * sizeof(T);
+        const bool three_fit = 7 * rb + 1024 <= 220 * 1024, two_fit = 5 * rb + 1024 <= 220 * 1024;
+        if ((flags & IA_IMPL_ADD_STAGED) && two_fit) return tma_flags_s<T, 2, false, kAddStaged>(p, variant, flags, s);
+        if (p.nvec >= 8192 || !three_fit) return tma_flags_s<T, 2, false, kAddLoaded>(p, variant, flags, s);
+        return tma_flags_s<T, 2, true, kAddStaged>(p, variant, flags, s);
     }
-    if (p.nvec >= 8192) return tma_flags_s<T, 2, false, false>(p, variant, flags, s);
-    return tma_flags_s<T, 2, true, false>(p, variant, flags, s);
+    if (p.nvec >= 8192) return tma_flags_s<T, 2, false, kAddNone>(p, variant, flags, s);
+    return tma_flags_s<T, 2, true, kAddNone>(p, variant, flags, s);
 }
 
 int launch_k2_tma(const K2Params &p, int dtype, int vec_dtype, int variant, int flags, cudaStream_t s) {

@@ -10,7 +10,7 @@ from typing import Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import (IA_BF16, IA_F16, IA_F32, IA_IMPL_REGS, IA_IMPL_TMA, IA_MODE_BASELINE, IA_MODE_POSNEG, IA_MODE_RAW,
+from ._lib import (IA_BF16, IA_F16, IA_F32, IA_IMPL_ADD_STAGED, IA_IMPL_REGS, IA_IMPL_TMA, IA_MODE_BASELINE, IA_MODE_POSNEG, IA_MODE_RAW,
                    IA_MODE_SIMPLE, IA_NORM_GEMMA, IA_NORM_LLAMA, IA_RSQRT_IEEE, IA_STEER_ALL, check)
 
 _DTYPES = {torch.bfloat16: IA_BF16, torch.float16: IA_F16, torch.float32: IA_F32}
@@ -56,7 +56,7 @@ def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: s
     rows, t_len, hid = h.shape
     y = torch.empty_like(h) if out is None else out
     flags = ((IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
-             | {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS}[impl])
+             | {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS, "add_staged": IA_IMPL_ADD_STAGED}[impl])
     lib = _lib.load()
     if add is not None:
         if add.shape != h.shape:

@@ -293,7 +293,10 @@ def test_residual_add_form_bit_exact_against_oracle(dt, variant):
     from introspective_awareness_b200 import kernels
 
     dev = _dev()
-    shapes = [(5, 3, 128), (4, 9, 896), (4, 3, 3584), (9, 2, 4096), (3, 3, 5120), (700, 3, 256), (1, 1, 132), (3, 2, 1000)]
+    # (3000, 3, 256) is a long launch (>= 8192 vectors): branch row through registers, one-row stages;
+    # the shorter ones stage it by bulk copy; H = 132 / 1000 take the two-pass kernel
+    shapes = [(5, 3, 128), (4, 9, 896), (4, 3, 3584), (9, 2, 4096), (3, 3, 5120), (700, 3, 256), (1, 1, 132), (3, 2, 1000),
+              (3000, 3, 256), (2100, 4, 1024)]
     for k, (rows, T, H) in enumerate(shapes):
         if dt == "f32" and H > 4096:
             continue
@@ -314,10 +317,13 @@ def test_residual_add_form_bit_exact_against_oracle(dt, variant):
                     kw = dict(vtable=torch.from_numpy(vt_m).to(dev) if vec_f32 else to_model(vt_m, dt, dev),
                               row_vec=torch.from_numpy(row_vec).to(dev), row_alpha=torch.from_numpy(alpha).to(dev),
                               row_t0=torch.from_numpy(t0).to(dev), pos0=pos0, steer_all=steer_all)
-                y = kernels.inject_rmsnorm(h_t, to_model(w, dt, dev), eps, variant, ieee_rsqrt=True, add=add_t, **kw)
-                torch.cuda.synchronize()
-                assert np.array_equal(h_t.float().cpu().numpy(), want_h), (dt, variant, rows, T, H, steer_all, steered, vec_f32)
-                assert np.array_equal(y.float().cpu().numpy(), want_y), (dt, variant, rows, T, H, steer_all, steered, vec_f32)
+                for impl in (("auto", "add_staged") if rows * T >= 8192 and not vec_f32 else ("auto",)):
+                    h_t = to_model(h, dt, dev)
+                    y = kernels.inject_rmsnorm(h_t, to_model(w, dt, dev), eps, variant, ieee_rsqrt=True, add=add_t, impl=impl, **kw)
+                    torch.cuda.synchronize()
+                    tag = (dt, variant, rows, T, H, steer_all, steered, vec_f32, impl)
+                    assert np.array_equal(h_t.float().cpu().numpy(), want_h), tag
+                    assert np.array_equal(y.float().cpu().numpy(), want_y), tag
                 assert torch.equal(add_t, to_model(add, dt, dev))  # the branch output is only read
 
 

@@ -48,7 +48,7 @@ def time_launch(fn, reps, flush):
     return total / reps
 
 
-def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16):
+def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16, add=False, add_staged=False):
     dev = torch.device("cuda:0")
     g = torch.Generator(device=dev).manual_seed(0)
     h = torch.randn(rows, T, H, device=dev, generator=g).to(dtype)
@@ -62,18 +62,25 @@ def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16):
 
     lib = _lib.load()
     flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS}[impl]
+    if add_staged:
+        flags |= _lib.IA_IMPL_ADD_STAGED
     args = (h.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(), t0.data_ptr(),
             w.data_ptr(), 1e-5, rows, T, H, 0, kernels._dt(h), kernels._dt(vt), kernels.VARIANTS[variant], flags,
             torch.cuda.current_stream().cuda_stream)
 
+    branch = (torch.randn(rows, T, H, device=dev, generator=g) * 1e-3).to(dtype) if add else None
+    if add:
+        # residual-add form: h <- h + branch first; five streams per vector (h, branch, table row, h', y)
+        args = args[:1] + (branch.data_ptr(),) + args[1:]
+
     def fn():  # the raw C-ABI call: no per-call Python tensor work inside the timed region
-        rc = lib.ia_inject_rmsnorm(*args)
+        rc = lib.ia_add_inject_rmsnorm(*args) if add else lib.ia_inject_rmsnorm(*args)
         assert rc == 0, rc
 
     ms = time_launch(fn, reps, flush)
-    algo = rows * T * H * e * 4 + H * e
-    return dict(kernel="k2_inject_rmsnorm", impl=impl, variant=variant, rows=rows, T=T, H=H, bytes=algo,
-                us=ms * 1e3, gbs=algo / ms / 1e6)
+    algo = rows * T * H * e * (5 if add else 4) + H * e
+    return dict(kernel="k2_add_inject_rmsnorm" if add else "k2_inject_rmsnorm", impl=impl, variant=variant, rows=rows, T=T,
+                H=H, bytes=algo, us=ms * 1e3, gbs=algo / ms / 1e6)
 
 
 def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16, want_norm=False):
@@ -110,11 +117,14 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only-rows", type=int, default=0, help="run a single cold K2 shape (for ncu --set full)")
     ap.add_argument("--only-k1", action="store_true", help="run only the K1 ladder")
+    ap.add_argument("--add", action="store_true", help="K2 in its residual-add form (ia_add_inject_rmsnorm)")
+    ap.add_argument("--add-staged", action="store_true", help="with --add: force the bulk-copied branch row (IA_IMPL_ADD_STAGED)")
     args = ap.parse_args()
     peak, src = peak_gbs()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda:0")
     if args.only_rows:
-        r = bench_k2(args.only_rows, 1, 4096, "llama", args.impl, args.reps, flush)
+        r = bench_k2(args.only_rows, 1, 4096, "llama", args.impl, args.reps, flush, add=args.add, add_staged=args.add_staged)
+        r["add_staged"] = args.add_staged
         r.update(cache="cold", frac=r["gbs"] / peak, peak=peak, peak_src=src)
         print(json.dumps(r), flush=True)
         return
@@ -129,9 +139,10 @@ def main():
             for cache, fl in (("cold", flush), ("hot", None)):
                 if cache == "hot" and rows * H * 2 * 3 > 100e6:
                     continue  # larger than L2 anyway
-                r = bench_k2(rows, 1, H, "gemma" if H == 3584 else "llama", args.impl, args.reps, fl)
-                r.update(cache=cache, frac=r["gbs"] / peak, peak=peak, peak_src=src)
-                print(json.dumps(r), flush=True)
+                for with_add in ((False, True) if H != 3584 else (False,)):  # Gemma-2 keeps the HF block
+                    r = bench_k2(rows, 1, H, "gemma" if H == 3584 else "llama", args.impl, args.reps, fl, add=with_add)
+                    r.update(cache=cache, frac=r["gbs"] / peak, peak=peak, peak_src=src)
+                    print(json.dumps(r), flush=True)
     for (L, C, Nb) in ([(32, 50, 100)] if args.quick else [(1, 50, 100), (32, 50, 100), (1, 50, 16334), (1, 50, 262094)]):
         r = bench_k1(L, C, Nb, 4096, args.reps, flush)
         r.update(frac=r["gbs"] / peak, peak=peak, peak_src=src)
