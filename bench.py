@@ -54,10 +54,12 @@ def peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_from_profiles():
-    """dram read+write bytes per launch of the prompt-pass K2, from the committed ncu summary."""
+def traffic_from_profiles(add_form: bool = False):
+    """dram read+write bytes per launch of the prompt-pass K2, from the committed ncu summary of the form
+    that was launched (plain, or with the residual add folded in)."""
     try:
-        d = json.load(open(os.path.join(ROOT, "profiles", "k2_prefill_ncu_summary.json")))
+        name = "k2_add_prefill_ncu_summary.json" if add_form else "k2_prefill_ncu_summary.json"
+        d = json.load(open(os.path.join(ROOT, "profiles", name)))
         return float(d["dram_bytes_per_launch"])
     except Exception:
         return None
@@ -306,7 +308,7 @@ def run_ours(args):
                                     "ia_inject_rmsnorm (ia::k2_tma_kernel: fused inject+RMSNorm, cp.async.bulk staged), prompt-pass launch"),
                          "bound": "hbm",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
-                         "traffic": traffic_from_profiles(), "peak_source": peak_src,
+                         "traffic": traffic_from_profiles(eng.native_block), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo, "us_per_launch": k2_avg_ms * 1e3,
                          "steered_fraction_of_vectors": steered_vecs / (rows * T_PROMPT),
                          "bytes_moved_per_launch": moved,
@@ -321,8 +323,9 @@ def run_ours(args):
                                  "(bytes_moved_per_launch, frac_of_peak_on_bytes_moved); the branch output was also just "
                                  "written by the preceding GEMM (partly L2-resident). Cold-cache, every-vector-steered "
                                  "figures for the same shape: tools/kbench.py -> profiles/r1_kbench_ladder.jsonl; `traffic` "
-                                 "is the DRAM byte count of the 4-stream kernel's ncu capture "
-                                 "(profiles/k2_prefill_ncu_summary.json)"},
+                                 "is the DRAM byte count per launch from the ncu --set full capture of the launched form "
+                                 "(profiles/k2_add_prefill_ncu_summary.json with the residual add, else "
+                                 "profiles/k2_prefill_ncu_summary.json)"},
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
