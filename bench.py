@@ -305,6 +305,8 @@ def run_ours(args):
             "gpu_launches": launches, "gpu_launches_by_kernel": launches_by_kernel,
             "roofline": {"kernel": ("ia_add_inject_rmsnorm (ia::k2_tma_kernel, ADD form: residual add + inject + RMSNorm, cp.async.bulk "
                                     "staged), prompt-pass launch" if eng.native_block else
+                                    "ia_gemma2_tail_inject_rmsnorm (ia::k2_tma_kernel, tail form: post-FFN norm + residual add + inject + "
+                                    "next RMSNorm, cp.async.bulk staged), prompt-pass launch" if tail else
                                     "ia_inject_rmsnorm (ia::k2_tma_kernel: fused inject+RMSNorm, cp.async.bulk staged), prompt-pass launch"),
                          "bound": "hbm",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,

@@ -320,6 +320,15 @@ extern "C" int ia_gemma2_tail_inject_rmsnorm(const void *mlp_out, void *residual
     p.h = residual; p.y = y; p.mlp = mlp_out; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
     p.row_t0 = row_t0; p.w = w_next; p.w_post = w_post; p.eps = eps; p.inv_h = 1.0f / (float)H;
     p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
+    // Bulk-copy staged form (MLP-output row staged, residual row through registers) where both weight rows
+    // and two one-row stages per warp fit; measured 2x the register form at 25 600 x 3584.
+    const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
+    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 4 + 1024 <= 220 * 1024;
+    if (flags & IA_IMPL_TMA) {
+        if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
+    }
+    if (tma_ok && !(flags & IA_IMPL_REGS))
+        return launch_k2_tma(p, dtype, vec_dtype, IA_NORM_GEMMA, flags, static_cast<cudaStream_t>(stream));
     return dispatch_dtype<true>(p, dtype, vec_dtype, IA_NORM_GEMMA, flags, static_cast<cudaStream_t>(stream));
 }
 

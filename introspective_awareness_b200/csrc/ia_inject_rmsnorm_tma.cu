@@ -71,7 +71,9 @@ template <typename T> __device__ __forceinline__ RowMeta load_meta(const K2Param
 // bulk-copied into the stage next to the residual row (short launches: everything arrives behind one
 // barrier).  kAddLoaded: it comes through registers with batched loads, the stage stays one row and
 // twice as many warps fit (long launches).
-constexpr int kAddNone = 0, kAddStaged = 1, kAddLoaded = 2;
+// kTail (Gemma-2 block tail): the staged row is the MLP output; it is normed with w_post first, the residual
+// row comes through registers like kAddLoaded, h = rd(residual + gemma_norm(mlp_out)), then as before.
+constexpr int kAddNone = 0, kAddStaged = 1, kAddLoaded = 2, kTail = 3;
 
 template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, int ADD>
 __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
@@ -82,14 +84,17 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     // layout: [weight row][mbarriers: nwarps*S x 8 B, padded to 128][stages: nwarps x S x (h row + v row)]
     T *w_s = reinterpret_cast<T *>(smem);
-    const unsigned bars_off = (row_bytes + 127u) & ~127u;
+    T *wpost_s = w_s + H;  // kTail only: second weight row
+    const unsigned bars_off = ((ADD == kTail ? 2u : 1u) * row_bytes + 127u) & ~127u;
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem + bars_off) + warp * S;
     const unsigned stage_off = bars_off + ((unsigned)(nwarps * S * 8 + 127) & ~127u);
     constexpr int kRowsPerStage = 1 + (ADD == kAddStaged ? 1 : 0) + (STAGE_V ? 1 : 0);
     unsigned char *my_stage = smem + stage_off + (size_t)warp * S * kRowsPerStage * row_bytes;
 
-    for (int g = threadIdx.x; g < G; g += blockDim.x)
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
         cp_async_group<sizeof(Pack4<T>)>(w_s + 4 * g, static_cast<const T *>(p.w) + 4 * g);
+        if (ADD == kTail) cp_async_group<sizeof(Pack4<T>)>(wpost_s + 4 * g, static_cast<const T *>(p.w_post) + 4 * g);
+    }
     if (lane == 0) {
         for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
         fence_proxy_async();  // make the initialised barriers visible to the async (TMA) proxy
@@ -110,7 +115,7 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
             fence_proxy_async();  // earlier generic-proxy accesses to this stage are done (warp synced)
             const bool with_v = STAGE_V && m.steer;
             mbar_expect_tx(&bars[stage], (1u + (ADD == kAddStaged ? 1u : 0u) + (with_v ? 1u : 0u)) * row_bytes);
-            bulk_g2s(dst, hbase + (size_t)v * H, row_bytes, &bars[stage]);
+            bulk_g2s(dst, (ADD == kTail ? static_cast<const T *>(p.mlp) : hbase) + (size_t)v * H, row_bytes, &bars[stage]);
             if (ADD == kAddStaged) bulk_g2s(dst + row_bytes, abase + (size_t)v * H, row_bytes, &bars[stage]);
             // (an L2 bulk prefetch of the register-loaded branch row here was measured slower: 177 vs 168 us at 25 600 x 4096)
             if (with_v) bulk_g2s(dst + (ADD == kAddStaged ? 2 : 1) * row_bytes, vtab + (size_t)m.vi * H, row_bytes, &bars[stage]);
@@ -149,7 +154,14 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
         const Injector<T, T> inj(cur.alpha);
 
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-        if (STAGE_V && cur.steer) {
+        float rm = 0.f;  // kTail: 1/rms of the MLP output row
+        if (ADD == kTail) {
+#pragma unroll 4
+            for (int g = lane; g < G; g += 32) sumsq4<T>(ld4<T>(h_s + 4 * g), a0, a1, a2, a3);
+            rm = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
+            a0 = a1 = a2 = a3 = 0.f;
+        }
+        if (ADD != kTail && STAGE_V && cur.steer) {
 #pragma unroll 4
             for (int g = lane; g < G; g += 32) {
                 Pack4<T> x = ld4<T>(h_s + 4 * g);
@@ -165,13 +177,18 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
             // through registers, 8 loads each in flight per lane (the stores below would otherwise keep the
             // compiler from hoisting them)
             const T *vp = vtab + (size_t)(cur.steer ? cur.vi : 0) * H;
-            const T *ap = abase + (size_t)vec * H;
+            const T *ap = (ADD == kTail ? hbase : abase) + (size_t)vec * H;
             for (int g0 = lane; g0 < G; g0 += 32 * 8) {
                 Pack4<T> vv[8], aa[8];
                 if (ADD == kAddLoaded) {
 #pragma unroll
                     for (int u = 0; u < 8; ++u)
                         if (g0 + 32 * u < G) aa[u] = ld4_ro<T>(ap + 4 * (g0 + 32 * u));
+                }
+                if (ADD == kTail) {  // the residual row is rewritten below: ordinary loads, not the read-only path
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (g0 + 32 * u < G) aa[u] = ld4<T>(ap + 4 * (g0 + 32 * u));
                 }
                 if (cur.steer) {
 #pragma unroll
@@ -185,6 +202,12 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
                         Pack4<T> x = ld4<T>(h_s + 4 * g);
                         if (ADD == kAddStaged) add4<T>(x, ld4<T>(a_s + 4 * g));
                         if (ADD == kAddLoaded) add4<T>(x, aa[u]);
+                        if (ADD == kTail) {
+                            Pack4<T> n;
+                            norm4<T, IA_NORM_GEMMA>(x, rm, ld4<T>(wpost_s + 4 * g), n);
+                            x = aa[u];
+                            add4<T>(x, n);
+                        }
                         if (cur.steer) inj.apply(x, vv[u]);
                         st4<T>(hp + 4 * g, x);
                         st4<T>(h_s + 4 * g, x);
@@ -215,14 +238,15 @@ template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, int ADD> stat
     const size_t row_bytes = (size_t)p.H * sizeof(T);
     const size_t budget = 220 * 1024;
     constexpr int kRowsPerStage = 1 + (ADD == kAddStaged ? 1 : 0) + (STAGE_V ? 1 : 0);
-    if (row_bytes + 1024 + kRowsPerStage * S * row_bytes > budget) return IA_ERR_TOO_LARGE;
-    int nwarps = (int)((budget - row_bytes - 1024) / (kRowsPerStage * S * row_bytes));
+    const size_t wrows = ADD == kTail ? 2 : 1;
+    if (wrows * row_bytes + 1024 + kRowsPerStage * S * row_bytes > budget) return IA_ERR_TOO_LARGE;
+    int nwarps = (int)((budget - wrows * row_bytes - 1024) / (kRowsPerStage * S * row_bytes));
     if (nwarps > 16) nwarps = 16;
     const int sms = sm_count();
     // small problems: do not start more warps than there are vectors per SM
     const int per_sm = (p.nvec + sms - 1) / sms;
     if (nwarps > per_sm) nwarps = per_sm < 1 ? 1 : per_sm;
-    const size_t bars_off = (row_bytes + 127) & ~(size_t)127;
+    const size_t bars_off = (wrows * row_bytes + 127) & ~(size_t)127;
     const size_t smem = bars_off + (((size_t)nwarps * S * 8 + 127) & ~(size_t)127) + (size_t)nwarps * kRowsPerStage * S * row_bytes;
     auto kern = k2_tma_kernel<T, VARIANT, IEEE, S, STAGE_V, ADD>;
     // opt in to large dynamic shared memory once per instantiation and device (first call = a warm-up
@@ -254,6 +278,10 @@ template <typename T> static int tma_flags(const K2Params &p, int variant, int f
     // Long launches: table rows come from L2 and a stage holds only the residual row, which doubles the
     // warps per SM (12 at H = 4096) — measured 1.29 vs 1.18 of the copy-bandwidth peak at 262 144 vectors.
     // Short launches are latency-bound: there the table row rides in the stage (10.4 vs 12.9 us at 200).
+    if (p.mlp) {  // Gemma-2 block tail
+        if (variant != IA_NORM_GEMMA) return IA_ERR_DTYPE;
+        return tma_flags_s<T, 2, false, kTail>(p, variant, flags, s);
+    }
     if (p.add) {
         // long launches: one-row stages (12 warps at H = 4096), branch and table rows through registers;
         // short launches: all three rows ride in the stage behind one barrier

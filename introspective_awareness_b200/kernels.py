@@ -80,12 +80,13 @@ def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: s
 def gemma2_tail_inject_rmsnorm(mlp_out: torch.Tensor, residual: torch.Tensor, w_post: torch.Tensor,
                                w_next: torch.Tensor, eps: float, vtable=None, row_vec=None, row_alpha=None,
                                row_t0=None, pos0: int = 0, steer_all: bool = False,
-                               out: Optional[torch.Tensor] = None, ieee_rsqrt: bool = False) -> torch.Tensor:
+                               out: Optional[torch.Tensor] = None, ieee_rsqrt: bool = False, impl: str = "auto") -> torch.Tensor:
     """K2 Gemma-2 block tail: residual <- inject(residual + gemma_norm(mlp_out; w_post)), returns
     gemma_norm(residual; w_next)."""
     rows, t_len, hid = residual.shape
     y = torch.empty_like(residual) if out is None else out
-    flags = (IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
+    flags = ((IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
+             | {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS}[impl])
     lib = _lib.load()
     rc = lib.ia_gemma2_tail_inject_rmsnorm(
         _cuda(mlp_out, "mlp_out", residual.dtype), _cuda(residual, "residual"), _cuda(y, "out", residual.dtype),

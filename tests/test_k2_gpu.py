@@ -225,12 +225,13 @@ def test_against_reference_fixtures(name):
 
 @pytest.mark.parametrize("dt", ["bf16", "f32"])
 def test_gemma2_tail_variant_against_oracle(dt):
+    """Both implementations: register-resident ("regs") and bulk-copy staged ("tma", the default where it fits:
+    MLP-output row staged, residual row through registers), including a run long enough for many ring
+    wrap-arounds per warp and, for fp32, a row wider than the register form covers."""
     from introspective_awareness_b200 import kernels
 
     dev = _dev()
-    for k, (rows, T, H) in enumerate([(4, 3, 128), (5, 2, 3584), (3, 2, 1024), (18, 1, 3584)]):
-        if dt == "f32" and H > 2048:
-            continue
+    for k, (rows, T, H) in enumerate([(4, 3, 128), (5, 2, 3584), (3, 2, 1024), (18, 1, 3584), (900, 3, 256)]):
         h, vt, vt_m, w, row_vec, alpha, t0 = make_inputs(rows, T, H, dt, 300 + k, gemma=True)
         rng = np.random.default_rng(k)
         mlp = K.rd(rng.standard_normal((rows, T, H)).astype(np.float32) * 3, dt)
@@ -238,14 +239,19 @@ def test_gemma2_tail_variant_against_oracle(dt):
         eps = 1e-6
         base = K.gemma2_block_tail(mlp, h, w_post, eps, dt)
         want_h, want_y = K.inject_rmsnorm(base, vt_m, row_vec, alpha, t0, 0, False, w, eps, "gemma", dt)
-        res_t = to_model(h, dt, dev)
-        y = kernels.gemma2_tail_inject_rmsnorm(
-            to_model(mlp, dt, dev), res_t, to_model(w_post, dt, dev), to_model(w, dt, dev), eps,
-            vtable=to_model(vt_m, dt, dev), row_vec=torch.from_numpy(row_vec).to(dev),
-            row_alpha=torch.from_numpy(alpha).to(dev), row_t0=torch.from_numpy(t0).to(dev), ieee_rsqrt=True)
-        torch.cuda.synchronize()
-        assert np.array_equal(res_t.float().cpu().numpy(), want_h), (dt, rows, T, H)
-        assert np.array_equal(y.float().cpu().numpy(), want_y), (dt, rows, T, H)
+        for impl in ("auto", "tma", "regs"):
+            if impl == "regs" and dt == "f32" and H > 2048:
+                continue  # the register form keeps an fp32 row of at most 2048 elements
+            res_t = to_model(h, dt, dev)
+            mlp_t = to_model(mlp, dt, dev)
+            y = kernels.gemma2_tail_inject_rmsnorm(
+                mlp_t, res_t, to_model(w_post, dt, dev), to_model(w, dt, dev), eps,
+                vtable=to_model(vt_m, dt, dev), row_vec=torch.from_numpy(row_vec).to(dev),
+                row_alpha=torch.from_numpy(alpha).to(dev), row_t0=torch.from_numpy(t0).to(dev), ieee_rsqrt=True, impl=impl)
+            torch.cuda.synchronize()
+            assert np.array_equal(res_t.float().cpu().numpy(), want_h), (dt, rows, T, H, impl)
+            assert np.array_equal(y.float().cpu().numpy(), want_y), (dt, rows, T, H, impl)
+            assert torch.equal(mlp_t, to_model(mlp, dt, dev))  # the MLP output is only read
 
 
 def test_full_size_properties():

@@ -83,6 +83,33 @@ def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16, add=F
                 H=H, bytes=algo, us=ms * 1e3, gbs=algo / ms / 1e6)
 
 
+def bench_tail(rows, H, impl, reps, flush, dtype=torch.bfloat16):
+    """Gemma-2 block tail (ia_gemma2_tail_inject_rmsnorm): five streams per vector."""
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(0)
+    res = torch.randn(rows, 1, H, device=dev, generator=g).to(dtype)
+    mlp = torch.randn(rows, 1, H, device=dev, generator=g).to(dtype)
+    y = torch.empty_like(res)
+    vt = (torch.randn(50, H, device=dev, generator=g) * 0.1).to(dtype)
+    w = torch.zeros(H, device=dev, dtype=dtype)
+    row_vec = (torch.arange(rows, device=dev) % 50).to(torch.int32)
+    alpha = torch.full((rows,), 4.0, device=dev)
+    t0 = torch.zeros(rows, device=dev, dtype=torch.int32)
+    lib = _lib.load()
+    flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS}[impl]
+    args = (mlp.data_ptr(), res.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(), t0.data_ptr(),
+            w.data_ptr(), w.data_ptr(), 1e-6, rows, 1, H, 0, kernels._dt(res), kernels._dt(vt), flags,
+            torch.cuda.current_stream().cuda_stream)
+
+    def fn():
+        rc = lib.ia_gemma2_tail_inject_rmsnorm(*args)
+        assert rc == 0, rc
+
+    ms = time_launch(fn, reps, flush)
+    algo = rows * H * res.element_size() * 5 + 2 * H * res.element_size()
+    return dict(kernel="k2_gemma2_tail", impl=impl, rows=rows, T=1, H=H, bytes=algo, us=ms * 1e3, gbs=algo / ms / 1e6)
+
+
 def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16, want_norm=False):
     dev = torch.device("cuda:0")
     g = torch.Generator(device=dev).manual_seed(0)
@@ -143,6 +170,12 @@ def main():
                     r = bench_k2(rows, 1, H, "gemma" if H == 3584 else "llama", args.impl, args.reps, fl, add=with_add)
                     r.update(cache=cache, frac=r["gbs"] / peak, peak=peak, peak_src=src)
                     print(json.dumps(r), flush=True)
+    if not args.only_k1:
+        for rows in ([25600] if args.quick else [200, 25600, 262144]):
+            for impl in ("auto", "regs"):
+                r = bench_tail(rows, 3584, impl, args.reps, flush)
+                r.update(cache="cold", frac=r["gbs"] / peak, peak=peak, peak_src=src)
+                print(json.dumps(r), flush=True)
     for (L, C, Nb) in ([(32, 50, 100)] if args.quick else [(1, 50, 100), (32, 50, 100), (1, 50, 16334), (1, 50, 262094)]):
         r = bench_k1(L, C, Nb, 4096, args.reps, flush)
         r.update(frac=r["gbs"] / peak, peak=peak, peak_src=src)
