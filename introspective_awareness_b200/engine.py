@@ -198,7 +198,8 @@ class DecoderEngine:
         # KV append, SiLU-gate multiply) and q/k/v and gate/up run as one GEMM each where that is
         # bit-identical to the separate ones on this device (checked per shape, see `_fused_ok`).
         self.native_block = (self.device.type == "cuda" and not self.is_gemma2 and self.hidden % 4 == 0
-                             and self.head_dim % 16 == 0 and getattr(cfg, "hidden_act", None) == "silu"
+                             and self.head_dim % 16 == 0 and getattr(cfg, "intermediate_size", 0) % 8 == 0
+                             and getattr(cfg, "hidden_act", None) == "silu"
                              and all(hasattr(first.self_attn, n) for n in ("q_proj", "k_proj", "v_proj", "o_proj"))
                              and all(hasattr(first.mlp, n) for n in ("gate_proj", "up_proj", "down_proj")))
         self.fuse_projections = True
