@@ -229,3 +229,31 @@ def test_empty_inputs(wrapper):
     assert wrapper.generate_batch_with_multi_steering([], 1, []) == []
     assert vu.extract_concept_vectors_batch(wrapper, [], ["Sand"], layer_idx=1) == {}
     assert grid.layer_trials([], [1.0], n_injection=3) == []
+
+
+def test_fused_linear_shares_storage_and_keeps_module_outputs():
+    """`engine._FusedLinear`: q/k/v (or gate/up) as one GEMM over concatenated weights.  The modules' own
+    parameters become row slices of the concatenated buffer — nothing stored twice, values unchanged, so the
+    stock HF forward (the reference hook path) still computes what it computed before."""
+    import torch
+
+    from introspective_awareness_b200.engine import _FusedLinear
+    from introspective_awareness_b200.synthetic import build_model
+
+    model = build_model("tiny-qwen2", dtype=torch.float32, device="cpu", seed=5)  # Qwen2: q/k/v carry biases
+    att = model.model.layers[0].self_attn
+    mods = [att.q_proj, att.k_proj, att.v_proj]
+    x = torch.randn(3, 7, model.config.hidden_size, generator=torch.Generator().manual_seed(0))
+    with torch.no_grad():
+        before = [m(x) for m in mods]
+        weights_before = [m.weight.detach().clone() for m in mods]
+        fused = _FusedLinear(mods)
+        after = [m(x) for m in mods]
+        parts = fused(x)
+    base = fused.W.untyped_storage().data_ptr()
+    for m, w0, b0, a0, part in zip(mods, weights_before, before, after, parts):
+        assert m.weight.untyped_storage().data_ptr() == base and m.bias.untyped_storage().data_ptr() == fused.b.untyped_storage().data_ptr()
+        assert torch.equal(m.weight, w0) and torch.equal(b0, a0)          # same values, same module output
+        assert part.shape == a0.shape and torch.allclose(part, a0, rtol=1e-5, atol=1e-6)
+    assert sum(fused.sizes) == fused.W.shape[0] and set(k for k in model.state_dict() if "layers.0.self_attn" in k) >= {
+        "model.layers.0.self_attn.q_proj.weight", "model.layers.0.self_attn.k_proj.bias"}
