@@ -43,6 +43,18 @@ def layer_trials(concepts: Sequence[str], strengths: Sequence[float], n_injectio
     return rows
 
 
+# Chat templates of these registry names reject a system turn (reference detect_injected_thoughts.py:80-81).
+MODELS_WITHOUT_SYSTEM_ROLE = ["gemma_2b", "gemma_7b", "gemma2_2b", "gemma2_9b", "gemma2_27b", "gemma3_27b"]
+
+
+def filter_messages_for_model(messages: List[dict], model_name: str) -> List[dict]:
+    """Drop system turns for models whose template has no system role
+    (reference detect_injected_thoughts.py:84-99; applied at :1833, :1935, :2001 before templating)."""
+    if model_name in MODELS_WITHOUT_SYSTEM_ROLE:
+        return [m for m in messages if m.get("role") != "system"]
+    return messages
+
+
 def chunk(rows: Sequence[Trial], batch_size: int) -> Iterable[Sequence[Trial]]:
     for i in range(0, len(rows), batch_size):
         yield rows[i:i + batch_size]
@@ -62,7 +74,8 @@ def run_layer(model, layer_idx: int, vectors: Dict[str, torch.Tensor], rows: Seq
         for r in part:
             key = (r.trial, r.kind == "forced")
             if key not in prompt_cache:
-                p = su.format_trial_prompt(model, r.trial, forced=key[1])
+                msgs = filter_messages_for_model(su.trial_messages(r.trial, key[1]), getattr(model, "model_name", ""))
+                p = su.format_trial_prompt(model, r.trial, forced=key[1], messages=msgs)
                 prompt_cache[key] = (p, su.steering_start_position(model, p, r.trial, missing=0))
             p, t0 = prompt_cache[key]
             prompts.append(p)

@@ -57,6 +57,12 @@ def test_reference_driver_imports_against_this_package(monkeypatch):
     assert drv.get_baseline_words(drv.DEFAULT_N_BASELINE) == ia.vector_utils.get_baseline_words(100)
     msgs = [{"role": "system", "content": ""}, {"role": "user", "content": "x"}]
     assert drv.filter_messages_for_model(msgs, "gemma2_9b") == msgs[1:]
+    # our grid applies the same filter, from the same list, before templating
+    from introspective_awareness_b200 import grid
+
+    assert grid.MODELS_WITHOUT_SYSTEM_ROLE == drv.MODELS_WITHOUT_SYSTEM_ROLE
+    for name in ("gemma2_9b", "llama_8b", "gemma3_27b", "qwen_32b"):
+        assert grid.filter_messages_for_model(msgs, name) == drv.filter_messages_for_model(msgs, name)
     sys.modules.pop("eval_utils", None)
 
 
