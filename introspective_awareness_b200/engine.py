@@ -59,11 +59,45 @@ def _gqa_sdpa_forward(module, query, key, value, attention_mask, dropout: float 
     transformers' stock `sdpa_attention_forward` materialises K and V `num_key_value_groups` times
     (`repeat_kv`) whenever a mask is present, i.e. for every left-padded batch — at B=200 that is as
     many bytes per decode step as the model weights.  Same math, K/V read once."""
-    causal = query.shape[2] > 1 and attention_mask is None
+    b, nh, t, d = query.shape
+    nkv = key.shape[1]
+    if nkv != nh and d > 128:
+        return _gqa_folded(query, key, value, attention_mask, scaling), None
+    causal = t > 1 and attention_mask is None
     out = torch.nn.functional.scaled_dot_product_attention(
         query, key, value, attn_mask=attention_mask, dropout_p=0.0, scale=scaling, is_causal=causal,
-        enable_gqa=key.shape[1] != query.shape[1])
+        enable_gqa=nkv != nh)
     return out.transpose(1, 2).contiguous(), None
+
+
+def _fold_mask(m: torch.Tensor, g: int) -> torch.Tensor:
+    """[B, 1, T, L] -> [B, 1, g*T, L]: the same T rows once per query head of the group."""
+    b, one, t, L = m.shape
+    return m[:, :, None].expand(b, one, g, t, L).reshape(b, one, g * t, L)
+
+
+def _gqa_folded(query, key, value, attention_mask, scaling):
+    """Grouped-query attention for head sizes torch's grouped-query kernels do not take (Gemma-2: 256).
+    The g query heads that share a KV head are laid side by side along the QUERY-LENGTH axis of that KV
+    head — q [B, n_kv, g*T, D] against K/V [B, n_kv, L, D] — so the ordinary fused kernel runs with K/V read
+    in place.  Every query row still sees the same keys in the same order through the same kernel, which is
+    why the result equals the repeat_kv form; what disappears is the g-fold copy of K and V per layer.
+    The engine hands over prompt-pass masks already folded (once per forward); an unfolded one is folded here."""
+    b, nh, t, d = query.shape
+    nkv, L = key.shape[1], key.shape[2]
+    g = nh // nkv
+    q = query.reshape(b, nkv, g * t, d)
+    m = attention_mask
+    if m is None and t > 1:  # causal without padding: spell the mask out, the folded rows are not in causal order
+        m = torch.ones(t, L, dtype=torch.bool, device=query.device).tril(L - t)[None, None]
+        m = torch.where(m, torch.zeros((), dtype=query.dtype, device=query.device),
+                        torch.full((), float("-inf"), dtype=query.dtype, device=query.device))
+    if m is not None and t > 1 and m.shape[2] == t:
+        m = _fold_mask(m, g)
+    out = torch.nn.functional.scaled_dot_product_attention(q, key, value, attn_mask=m, dropout_p=0.0, scale=scaling,
+                                                           is_causal=False)
+    # [B, n_kv, g, T, D] -> [B, T, n_kv, g, D] = [B, T, n_heads, D]
+    return out.view(b, nkv, g, t, d).permute(0, 3, 1, 2, 4).reshape(b, t, nh, d).contiguous()
 
 
 def _register_attention():
@@ -284,6 +318,17 @@ class DecoderEngine:
         if self.additive_masks and args[0].is_cuda:
             args = list(args)
             args[2] = self._additive(args[2], args[0].dtype)
+        g = self.cfg.num_attention_heads // self.n_kv
+        if self.attention == "gqa" and self.head_dim > 128 and g > 1 and args[0].shape[1] > 1:
+            # folded grouped-query attention (`_gqa_folded`): fold the prompt-pass masks once, not per layer
+            args = list(args)
+            done = {}
+            t = args[0].shape[1]
+            for kind, m in list(args[2].items()):
+                if m is not None and m.shape[2] == t:
+                    if id(m) not in done:
+                        done[id(m)] = _fold_mask(m, g)
+                    args[2] = {**args[2], kind: done[id(m)]}
         try:
             return self._run_layers(*args, **kwargs)
         finally:
