@@ -172,11 +172,11 @@ class DecoderEngine:
     """Layer loop over a Hugging Face Llama / Qwen2 / Gemma-2 causal LM."""
 
     def __init__(self, model, fuse_gemma_tail: bool = True, attention: str = "hf", fused_norms: Optional[bool] = None):
-        """attention: "hf" keeps the model's own attention function (bit-identical to the reference
-        hook path on the same device); "gqa" swaps in `_gqa_sdpa_forward` (no repeat_kv copies);
-        "auto" = "gqa" when head_dim <= 128 (torch has a fused grouped-query kernel there: measured
-        3.2x faster decode on Llama-3.1-8B and still bit-identical), else "hf" (at Gemma-2's head_dim 256
-        the grouped-query call falls back to the unfused path and is slower than HF's).
+        """attention: "hf" keeps the model's own attention function; "gqa" (= "auto") swaps in
+        `_gqa_sdpa_forward`, which never materialises K/V per query head (HF's `repeat_kv`): torch's
+        grouped-query kernel where head_dim <= 128 (measured 3.2x faster decode on Llama-3.1-8B), the folded form
+        `_gqa_folded` above that (Gemma-2's 256: 1.9x faster bench step).  Both are bit-identical to the reference
+        hook path on the same device (tests/test_e2e_gpu.py).
         fused_norms: run every RMSNorm of the stack through K2 (one launch instead of torch's ~7
         eager kernels, same bits); default = on CUDA."""
         self.model = model
@@ -217,7 +217,7 @@ class DecoderEngine:
         self.fused_rope = self.device.type == "cuda"
         self._extract_graphs: Dict[tuple, tuple] = {}
         if attention == "auto":
-            attention = "gqa" if self.head_dim <= 128 else "hf"
+            attention = "gqa"
         self.attention = attention
         if attention == "gqa":
             _register_attention()

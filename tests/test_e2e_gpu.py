@@ -152,24 +152,18 @@ def test_same_device_hook_path_gemma2_9b_and_qwen_32b_dims(arch, layer, attentio
     """BASELINE configs[3]/[4] shapes: Gemma-2 (post+pre norm fusion variant, incl. injection at the
     LAST layer, fused with model.norm) and Qwen2.5-32B (H = 5120) against the hook path on the same GPU.
 
-    With the model's stock attention function every kernel of ours is on the path (K2 for all norms, the
-    Gemma-2 tail variant, fused rope) and the logits must satisfy north_star's 2e-2 — in fact they are
-    bit-identical.  The grouped-query SDPA mode picks a different torch attention kernel at
-    head_dim = 256, which moves Gemma's logits (|x| up to ~21, where one bf16 ulp is 0.125) by at most
-    one ulp: there the bound is one bf16 ulp at the scale of the largest logit, and identical greedy tokens."""
+    Every kernel of ours is on the path (K2 for all norms, the Gemma-2 tail variant, fused rope; for Qwen the
+    engine-driven block) and the logits must satisfy north_star's 2e-2 — in fact they are bit-identical, with the
+    model's stock attention function and with the grouped-query mode alike (at head_dim = 256 that is the folded
+    form, which runs the same fused kernel as HF's repeat_kv path with K/V read in place)."""
     # seed=None: Hugging Face's own initialisation, on the GPU (both paths share the model object)
     ours, ol, ref, rl = _hook_path_vs_ours(arch, layer, rows=96, t_max=64, t_min=48, n_new=32,
                                            alphas=[1.0, 2.0, 4.0, 8.0], seed=None, n_concepts=24, attention=attention)
     diff = (ol - rl).abs()
     same_rows = (ours == ref).all(dim=1).float().mean().item()
     print(f"{arch} L={layer} {attention}: max |logit diff| = {diff.max().item():.4g}; identical 32-token rows: {same_rows:.3f}")
-    if attention == "hf" or "qwen" in arch:
-        assert diff.max().item() <= 2e-2
-        assert torch.equal(ours, ref)
-    else:
-        same = (ours == ref).all(dim=1)
-        assert diff[:, same].max().item() <= rl.abs().max().item() * 2.0 ** -7  # one bf16 ulp at the logit scale
-        assert same.float().mean().item() >= 0.95
+    assert diff.max().item() == 0.0
+    assert torch.equal(ours, ref)
 
 
 def test_gqa_attention_mode_stays_within_tolerance():
@@ -268,7 +262,7 @@ def test_runtime_optimisations_do_not_change_bits(arch):
     """K2 for every RMSNorm, the fused rotary kernel, the Gemma-2 tail variant, grouped-query SDPA, the
     CUDA graphs, the once-per-forward mask conversion, the engine-driven Llama block (residual add inside K2,
     rotary + KV append, SiLU-gate multiply) and the single-GEMM q/k/v and gate/up projections, each switched
-    off in turn: same logits, bit for bit (Gemma-2's head_dim 256 grouped-query path excepted, see above)."""
+    off in turn: same logits, bit for bit (Gemma-2's grouped-query mode is checked at its real head size above)."""
     from introspective_awareness_b200.synthetic import synthetic_prompt_ids
 
     w = _wrapper(arch, torch.bfloat16, 9 if arch.startswith("tiny") else None, attention="hf")
