@@ -237,6 +237,7 @@ class DecoderEngine:
                              and all(hasattr(first.self_attn, n) for n in ("q_proj", "k_proj", "v_proj", "o_proj"))
                              and all(hasattr(first.mlp, n) for n in ("gate_proj", "up_proj", "down_proj")))
         self.fuse_projections = True
+        self.gemma_tail_everywhere = True   # Gemma-2: block-tail K2 at both residual joins of every layer
         self._qkv: Optional[list] = None   # per layer _FusedLinear, built on first use
         self._gu: Optional[list] = None
         self._fused_checked: Dict[tuple, bool] = {}
@@ -343,6 +344,8 @@ class DecoderEngine:
         With `stop_after` the loop ends after that layer and nothing is normed."""
         if self.native_block and h.is_cuda and self.fused_norms:
             return self._run_layers_native(h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture)
+        if self.is_gemma2 and self.fuse_gemma_tail and self.gemma_tail_everywhere and h.is_cuda and self.fused_norms:
+            return self._run_layers_gemma(h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture)
         captured: Dict[int, torch.Tensor] = {}
         want = set(capture or ())
         last = self.n_layers - 1 if stop_after is None else stop_after
@@ -502,6 +505,55 @@ class DecoderEngine:
             self.k2_events.append((ev[0], ev[1], h.numel() * h.element_size()))
         self.counters["k2_launches"] += 1
         return y
+
+    def _gemma_tail(self, branch, h, w_post, w_next, steer=None, pos0=0, decode=False, timed=False):
+        """h <- h + gemma_norm(branch; w_post) [+ alpha*v]; returns gemma_norm(h; w_next).  One launch for what the
+        HF layer does as norm kernel + add kernel (+ hook) + the next norm."""
+        ev = None
+        if timed and self.k2_events is not None and not decode:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
+        kw = {}
+        if steer is not None:
+            kw = dict(vtable=steer.vtable, row_vec=steer.row_vec, row_alpha=steer.row_alpha,
+                      row_t0=None if decode else steer.row_t0, pos0=pos0, steer_all=decode or steer.row_t0 is None)
+        y = kernels.gemma2_tail_inject_rmsnorm(branch if branch.is_contiguous() else branch.contiguous(), h, w_post, w_next,
+                                               self.eps, **kw)
+        if ev is not None:
+            ev[1].record()
+            self.k2_events.append((ev[0], ev[1], h.numel() * h.element_size()))
+        self.counters["k2_launches"] += 1
+        return y
+
+    def _run_layers_gemma(self, h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture):
+        """Gemma-2 with the block-tail form of K2 at BOTH residual joins of every layer (after attention:
+        post_attention_layernorm + add + pre_feedforward_layernorm; after the MLP: post_feedforward_layernorm + add
+        [+ injection] + the next layer's input_layernorm).  Attention and MLP stay the HF modules.  The residual
+        stream is one buffer updated in place."""
+        captured: Dict[int, torch.Tensor] = {}
+        want = set(capture or ())
+        last = self.n_layers - 1 if stop_after is None else stop_after
+        if not h.is_contiguous():
+            h = h.contiguous()
+        x = self.norm(self.layers[0].input_layernorm, h)
+        final = None
+        for i in range(last + 1):
+            layer = self.layers[i]
+            attn, _ = layer.self_attn(hidden_states=x, position_embeddings=pos_emb,
+                                      attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
+            x = self._gemma_tail(attn, h, layer.post_attention_layernorm.weight, layer.pre_feedforward_layernorm.weight)
+            m = layer.mlp(x)
+            st = steer if (steer is not None and steer.layer_idx == i) else None
+            nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
+            y = self._gemma_tail(m, h, layer.post_feedforward_layernorm.weight, nxt.weight, steer=st, pos0=pos0,
+                                 decode=decode, timed=st is not None)
+            if i < last:
+                x = y
+            elif stop_after is None:
+                final = y
+            if i in want:
+                captured[i] = h if i == last else h.clone()
+        return final, captured
 
     def _run_layers_native(self, h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture):
         """Same contract as `_run_layers`.  The residual stream `h` is ONE buffer updated in place by K2
