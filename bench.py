@@ -463,7 +463,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--arch", default=ARCH)
-    ap.add_argument("--cpu-rows", type=int, default=2)
+    ap.add_argument("--cpu-rows", type=int, default=8,
+                    help="steered trials per CPU step of the reference arm / cpu_baseline sample (batched like the reference batches)")
     ap.add_argument("--attention", default="auto", choices=["auto", "gqa", "hf"],
                     help="gqa: grouped-query SDPA without repeat_kv copies; hf: the model's stock attention function")
     ap.add_argument("--no-cpu-baseline", action="store_true")
