@@ -13,7 +13,8 @@
  *   - return value: 0 = enqueued; negative = argument error (IA_ERR_*), nothing was launched;
  *     positive = a cudaError_t raised by the launch;
  *   - stateless and thread-safe: calls on different streams may overlap as long as their
- *     buffers (including the workspace) do not.
+ *     buffers (including the workspace) do not — except ia_gather_meandiff_static, which keeps
+ *     process-wide state (one built-in scratch array per GPU; see its comment below).
  *
  * Element types.  `dtype` is the MODEL dtype (the residual stream and the norm weight);
  * all arithmetic is fp32 with results rounded to `dtype` exactly where the reference's torch
@@ -51,7 +52,9 @@ extern "C" {
 #define IA_IMPL_TMA 4    /* force the bulk-copy (TMA, cp.async.bulk + mbarrier) staged implementation */
 #define IA_IMPL_REGS 8   /* force the register-resident implementation */
 #define IA_IMPL_ADD_STAGED 16 /* ia_add_inject_rmsnorm: bulk-copy the branch row into the stage even in long launches */
-/* neither bit: automatic — TMA staging when a row is >= 4 KiB and the table is in the model dtype */
+#define IA_IMPL_STREAM 32 /* force the streaming implementation (row in registers, quarter-row bulk-copy landing slots) */
+/* no IMPL bit: automatic — streaming for launches of >= 8192 vectors (16-bit dtypes, H in 1024/2048/3584/4096/5120),
+ * TMA staging for shorter launches when a row is >= 4 KiB and the table is in the model dtype, else registers */
 
 /* extraction methods (ia_gather_meandiff / ia_meandiff_finalize `mode`) */
 #define IA_MODE_BASELINE 0 /* v_c = act_c - mean_b(act_b)      vector_utils.py:541-545           */
@@ -203,6 +206,31 @@ IA_API int ia_meandiff_finalize(const void *concept_acts, int64_t n_concept, con
                          void *workspace, int64_t workspace_bytes, int32_t dtype, void *stream);
 
 /*
+ * K1 from compact inputs — what the K2 tap entry points write: concept_acts [n_layers, n_concept, H] and
+ * base_acts [n_layers, n_base, H] (dtype, contiguous; base_acts ignored for IA_MODE_RAW).
+ *
+ * Replaces the same reference lines as ia_gather_meandiff — the capture hook's slice + `.cpu()` (reference
+ * model_utils.py:312-321, done by the tap) and the vector arithmetic of vector_utils.py:541-548, :570-573, :586-589,
+ * :103-109 — with no pointer table and no pass over the full residual tensors.  Same outputs, rounding points,
+ * summation order and workspace (ia_meandiff_workspace_bytes) as ia_gather_meandiff; bit-identical to it on the
+ * same rows.  For n_base <= 256 (the reference's 100 baseline words) this is ONE launch (+ the norm pass when
+ * normalize or out_norm asks for it): a warp per (layer, 256-column tile, share of the concept rows) streams its
+ * rows through a lane-private cp.async ring.
+ */
+IA_API int ia_meandiff_compact(const void *concept_acts, int64_t n_concept, const void *base_acts, int64_t n_base,
+                        int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,
+                        void *out_rounded, float *out_norm, void *workspace, int64_t workspace_bytes,
+                        int32_t dtype, void *stream);
+
+/*
+ * K1a from compact rows: fp32 column sums out_sum [n_layers, H] of rows [n_layers, n_rows, H] (dtype), in the
+ * chunked sequential order of ia_gather_segsum — the rank-local half of prompt-sharded extraction when the rows
+ * were captured by the K2 tap.  No reference counterpart beyond the lines cited for K1 (no data parallelism there).
+ */
+IA_API int ia_segsum_compact(const void *rows, int64_t n_rows, int64_t n_layers, int64_t H, float *out_sum,
+                      void *workspace, int64_t workspace_bytes, int32_t dtype, void *stream);
+
+/*
  * Runtime support (not a hot-path row of SURVEY.md §8): rotary position embedding of q and k in one
  * launch, with the rounding points of transformers' apply_rotary_pos_emb
  * (modeling_llama.py; reached through reference model_utils.py:338 and :847 like every other model op):
@@ -226,6 +254,33 @@ IA_API int ia_add_inject_rmsnorm(void *h, const void *add, void *y, const void *
                           const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
                           int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype,
                           int32_t vec_dtype, int32_t variant, int32_t flags, void *stream);
+
+/*
+ * K2 with a capture tap — the three entry points above with one more output.
+ *
+ * Replaces, in addition to what the un-tapped entry point replaces: the capture hook of
+ * ModelWrapper.extract_activations (reference model_utils.py:312-321: slice the hooked layer output at
+ * token_idx, detach, `.cpu()`), for the layer whose output this launch finishes.  The kernel already has the
+ * row in hand when it writes it back, so the captured row costs one extra H-element store and no extra read:
+ *     cap_out[b, :] = h[b, p, :]  (the UPDATED row)   for p = (cap_tok ? cap_tok[b] : cap_t)
+ * cap_out [rows, H] (dtype, 16-byte aligned) is compact — what K1 (ia_meandiff_compact) consumes; cap_tok
+ * [rows] int32 or NULL; cap_t may be negative (-1 = last position, the reference's token_idx default).
+ * cap_out == NULL makes these identical to the un-tapped calls.
+ */
+IA_API int ia_inject_rmsnorm_tap(void *h, void *y, const void *vtable, const int32_t *row_vec, const float *row_alpha,
+                          const int32_t *row_t0, const void *w, float eps, int64_t rows, int64_t T, int64_t H,
+                          int32_t pos0, int32_t dtype, int32_t vec_dtype, int32_t variant, int32_t flags,
+                          void *cap_out, const int32_t *cap_tok, int32_t cap_t, void *stream);
+IA_API int ia_add_inject_rmsnorm_tap(void *h, const void *add, void *y, const void *vtable, const int32_t *row_vec,
+                              const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
+                              int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype, int32_t vec_dtype,
+                              int32_t variant, int32_t flags, void *cap_out, const int32_t *cap_tok,
+                              int32_t cap_t, void *stream);
+IA_API int ia_gemma2_tail_inject_rmsnorm_tap(const void *mlp_out, void *residual, void *y, const void *vtable,
+                                      const int32_t *row_vec, const float *row_alpha, const int32_t *row_t0,
+                                      const void *w_post, const void *w_next, float eps, int64_t rows, int64_t T,
+                                      int64_t H, int32_t pos0, int32_t dtype, int32_t vec_dtype, int32_t flags,
+                                      void *cap_out, const int32_t *cap_tok, int32_t cap_t, void *stream);
 
 /*
  * Runtime support: ia_rope plus the KV-cache append in the same launch.  q/k/v are [tokens, heads, head_dim]

@@ -14,7 +14,7 @@ HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "ia_b200.h")
 
 IA_BF16, IA_F16, IA_F32 = 0, 1, 2
 IA_NORM_LLAMA, IA_NORM_GEMMA = 0, 1
-IA_STEER_ALL, IA_RSQRT_IEEE, IA_IMPL_TMA, IA_IMPL_REGS, IA_IMPL_ADD_STAGED = 1, 2, 4, 8, 16
+IA_STEER_ALL, IA_RSQRT_IEEE, IA_IMPL_TMA, IA_IMPL_REGS, IA_IMPL_ADD_STAGED, IA_IMPL_STREAM = 1, 2, 4, 8, 16, 32
 IA_MODE_BASELINE, IA_MODE_SIMPLE, IA_MODE_RAW, IA_MODE_POSNEG = 0, 1, 2, 3
 
 
@@ -30,6 +30,15 @@ _SIGNATURES = {
     "ia_gemma2_tail_inject_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                               c_void_p, c_void_p, c_float, c_int64, c_int64, c_int64, c_int32,
                                               c_int32, c_int32, c_int32, c_void_p]),
+    "ia_inject_rmsnorm_tap": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                      c_int64, c_int64, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32,
+                                      c_void_p, c_void_p, c_int32, c_void_p]),
+    "ia_add_inject_rmsnorm_tap": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_float, c_int64, c_int64, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32,
+                                          c_void_p, c_void_p, c_int32, c_void_p]),
+    "ia_gemma2_tail_inject_rmsnorm_tap": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                  c_void_p, c_void_p, c_float, c_int64, c_int64, c_int64, c_int32,
+                                                  c_int32, c_int32, c_int32, c_void_p, c_void_p, c_int32, c_void_p]),
     "ia_meandiff_workspace_bytes": (c_int64, [c_int64, c_int64, c_int64, c_int64, c_int32]),
     "ia_gather_meandiff": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                    c_void_p, c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p, c_void_p,
@@ -38,6 +47,9 @@ _SIGNATURES = {
                                  c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "ia_meandiff_finalize": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int32, c_int32,
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
+    "ia_meandiff_compact": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
+    "ia_segsum_compact": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "ia_gather_meandiff_static": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                           c_void_p, c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p, c_void_p,
                                           c_void_p, c_int32, c_void_p]),

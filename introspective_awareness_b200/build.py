@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libia_b200.so")
-SOURCES = ["ia_abi.cu", "ia_inject_rmsnorm.cu", "ia_inject_rmsnorm_tma.cu", "ia_meandiff.cu", "ia_rope.cu", "ia_mlp_act.cu"]
+SOURCES = ["ia_abi.cu", "ia_inject_rmsnorm.cu", "ia_inject_rmsnorm_tma.cu", "ia_inject_rmsnorm_stream.cu", "ia_meandiff.cu", "ia_rope.cu", "ia_mlp_act.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",

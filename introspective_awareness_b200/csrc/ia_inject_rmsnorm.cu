@@ -119,6 +119,13 @@ __global__ void __launch_bounds__(128, MINB) k2_regs_kernel(const K2Params p) {
                 if (j < nj) st4<T>(hp + 4 * (lane + 32 * j), x[j]);
         }
 
+        if (tap_here(p, row, pos)) {  // extraction capture: the updated row, compactly
+            T *cp = static_cast<T *>(p.cap_out) + (size_t)row * H;
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j)
+                if (j < nj) st4<T>(cp + 4 * (lane + 32 * j), x[j]);
+        }
+
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
         for (int j = 0; j < MAXJ; ++j)
@@ -166,11 +173,13 @@ __global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
         const Injector<T, VT> inj(alpha);
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         const T *ap = p.add ? static_cast<const T *>(p.add) + (size_t)vec * H : nullptr;
+        T *cp = tap_here(p, row, pos) ? static_cast<T *>(p.cap_out) + (size_t)row * H : nullptr;
         for (int g = lane; g < G; g += 32) {
             Pack4<T> x = ld4<T>(hp + 4 * g);
             if (ap) add4<T>(x, ld4_ro<T>(ap + 4 * g));
             if (steer) inj.apply(x, ld4_ro<VT>(vp + 4 * g));
             if (steer || ap) st4<T>(hp + 4 * g, x);
+            if (cp) st4<T>(cp + 4 * g, x);
             sumsq4<T>(x, a0, a1, a2, a3);
         }
         const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
@@ -182,6 +191,8 @@ __global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
         }
     }
 }
+
+constexpr int kStreamMinVectors = 8192;  // below this a launch is latency-bound: the staged kernel's layout wins
 
 int sm_count() {
     static int cached[64] = {0};
@@ -277,32 +288,94 @@ static int check_common(const void *h, const void *y, const void *vtable, const 
     return 0;
 }
 
+// One body for the three K2 entry points and their tap forms.  `other` is the branch output (residual-add
+// form), the MLP output (Gemma-2 block tail, with w_post) or NULL (plain form).
+enum K2Form { kPlain = 0, kAddForm = 1, kTailForm = 2 };
+
+static int k2_entry(K2Form form, void *h, const void *other, void *y, const void *vtable, const int32_t *row_vec,
+                    const float *row_alpha, const int32_t *row_t0, const void *w_post, const void *w, float eps,
+                    int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype, int32_t vec_dtype, int32_t variant,
+                    int32_t flags, void *cap_out, const int32_t *cap_tok, int32_t cap_t, void *stream) {
+    if (form != kPlain && !other) return IA_ERR_NULL;
+    if (form == kTailForm && !w_post) return IA_ERR_NULL;
+    int rc = check_common(h, y, vtable, row_vec, row_alpha, row_t0, w, rows, T, H, flags);
+    if (rc) return rc;
+    if ((other && !aligned16(other)) || (w_post && !aligned16(w_post)) || (cap_out && !aligned16(cap_out))) return IA_ERR_ALIGN;
+    if (form == kTailForm) variant = IA_NORM_GEMMA;
+    if (variant != IA_NORM_LLAMA && variant != IA_NORM_GEMMA) return IA_ERR_DTYPE;
+    if (cap_out && !cap_tok) {
+        if (cap_t < 0) cap_t += (int32_t)T;  // -1 = the last position, as the reference's token_idx=-1
+        if (cap_t < 0 || cap_t >= T) return IA_ERR_SHAPE;
+    }
+    if (rows == 0) return 0;
+    K2Params p{};
+    p.h = h; p.y = y; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha; p.row_t0 = row_t0;
+    p.mlp = form == kTailForm ? other : nullptr;
+    p.add = form == kAddForm ? other : nullptr;
+    p.w = w; p.w_post = form == kTailForm ? w_post : nullptr;
+    p.eps = eps; p.inv_h = 1.0f / (float)H;
+    p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
+    p.cap_out = cap_out; p.cap_tok = cap_tok; p.cap_t = cap_t;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // Implementation choice (same bits every way).  Long launches (prompt passes): the streaming kernel — row
+    // in registers, quarter-row landing slots, every DRAM operand by bulk copy.  Rows of a few KiB in shorter
+    // launches: the bulk-copy staged kernel (lowest latency; measured 1.10 vs 0.95 of the copy-bandwidth peak
+    // against the register kernel at H = 4096).  Short rows, fp32 tables, other H: the register / two-pass kernels.
+    const bool stream_ok = k2_stream_supported(p, dtype, vec_dtype);
+    if (flags & IA_IMPL_STREAM) {
+        if (!stream_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
+        return launch_k2_stream(p, dtype, vec_dtype, variant, flags, s);
+    }
+    const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
+    // staged kernel: the weight row(s) and two stages per warp must fit in shared memory
+    const int64_t stage_rows = form == kPlain ? 5 : (form == kAddForm ? 3 : 4);
+    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * stage_rows + 1024 <= 220 * 1024;
+    if (flags & IA_IMPL_TMA) {
+        if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
+        return launch_k2_tma(p, dtype, vec_dtype, variant, flags, s);
+    }
+    if (!(flags & IA_IMPL_REGS)) {
+        if (stream_ok && p.nvec >= kStreamMinVectors) return launch_k2_stream(p, dtype, vec_dtype, variant, flags, s);
+        if (tma_ok && (form != kPlain || row_bytes >= 4096)) return launch_k2_tma(p, dtype, vec_dtype, variant, flags, s);
+    }
+    return form == kTailForm ? dispatch_dtype<true>(p, dtype, vec_dtype, variant, flags, s)
+                             : dispatch_dtype<false>(p, dtype, vec_dtype, variant, flags, s);
+}
+
 }  // namespace ia
+
+extern "C" int ia_inject_rmsnorm_tap(void *h, void *y, const void *vtable, const int32_t *row_vec, const float *row_alpha,
+                                     const int32_t *row_t0, const void *w, float eps, int64_t rows, int64_t T, int64_t H,
+                                     int32_t pos0, int32_t dtype, int32_t vec_dtype, int32_t variant, int32_t flags,
+                                     void *cap_out, const int32_t *cap_tok, int32_t cap_t, void *stream) {
+    return ia::k2_entry(ia::kPlain, h, nullptr, y, vtable, row_vec, row_alpha, row_t0, nullptr, w, eps, rows, T, H, pos0, dtype,
+                        vec_dtype, variant, flags, cap_out, cap_tok, cap_t, stream);
+}
+
+extern "C" int ia_add_inject_rmsnorm_tap(void *h, const void *add, void *y, const void *vtable, const int32_t *row_vec,
+                                         const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
+                                         int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype, int32_t vec_dtype,
+                                         int32_t variant, int32_t flags, void *cap_out, const int32_t *cap_tok,
+                                         int32_t cap_t, void *stream) {
+    return ia::k2_entry(ia::kAddForm, h, add, y, vtable, row_vec, row_alpha, row_t0, nullptr, w, eps, rows, T, H, pos0, dtype,
+                        vec_dtype, variant, flags, cap_out, cap_tok, cap_t, stream);
+}
+
+extern "C" int ia_gemma2_tail_inject_rmsnorm_tap(const void *mlp_out, void *residual, void *y, const void *vtable,
+                                                 const int32_t *row_vec, const float *row_alpha, const int32_t *row_t0,
+                                                 const void *w_post, const void *w_next, float eps, int64_t rows, int64_t T,
+                                                 int64_t H, int32_t pos0, int32_t dtype, int32_t vec_dtype, int32_t flags,
+                                                 void *cap_out, const int32_t *cap_tok, int32_t cap_t, void *stream) {
+    return ia::k2_entry(ia::kTailForm, residual, mlp_out, y, vtable, row_vec, row_alpha, row_t0, w_post, w_next, eps, rows, T, H,
+                        pos0, dtype, vec_dtype, IA_NORM_GEMMA, flags, cap_out, cap_tok, cap_t, stream);
+}
 
 extern "C" int ia_inject_rmsnorm(void *h, void *y, const void *vtable, const int32_t *row_vec,
                                  const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
                                  int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype,
                                  int32_t vec_dtype, int32_t variant, int32_t flags, void *stream) {
-    using namespace ia;
-    int rc = check_common(h, y, vtable, row_vec, row_alpha, row_t0, w, rows, T, H, flags);
-    if (rc) return rc;
-    if (variant != IA_NORM_LLAMA && variant != IA_NORM_GEMMA) return IA_ERR_DTYPE;
-    if (rows == 0) return 0;
-    K2Params p{};
-    p.h = h; p.y = y; p.mlp = nullptr; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
-    p.row_t0 = row_t0; p.w = w; p.w_post = nullptr; p.eps = eps; p.inv_h = 1.0f / (float)H;
-    p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
-    // Implementation choice (same bits either way): bulk-copy staging wins once a row is a few KiB
-    // (measured on B200: 1.10 vs 0.95 of the copy-bandwidth peak at H = 4096); short rows make its
-    // per-row barrier/issue overhead visible, so they stay on the register kernel.
-    const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
-    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 5 + 1024 <= 220 * 1024;
-    const bool want_tma = (flags & IA_IMPL_TMA) || (!(flags & IA_IMPL_REGS) && row_bytes >= 4096);
-    if (flags & IA_IMPL_TMA) {
-        if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
-    }
-    if (want_tma && tma_ok) return launch_k2_tma(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
-    return dispatch_dtype<false>(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
+    return ia_inject_rmsnorm_tap(h, y, vtable, row_vec, row_alpha, row_t0, w, eps, rows, T, H, pos0, dtype, vec_dtype, variant,
+                                 flags, nullptr, nullptr, 0, stream);
 }
 
 extern "C" int ia_gemma2_tail_inject_rmsnorm(const void *mlp_out, void *residual, void *y, const void *vtable,
@@ -310,50 +383,14 @@ extern "C" int ia_gemma2_tail_inject_rmsnorm(const void *mlp_out, void *residual
                                              const int32_t *row_t0, const void *w_post, const void *w_next,
                                              float eps, int64_t rows, int64_t T, int64_t H, int32_t pos0,
                                              int32_t dtype, int32_t vec_dtype, int32_t flags, void *stream) {
-    using namespace ia;
-    if (!mlp_out || !w_post) return IA_ERR_NULL;
-    int rc = check_common(residual, y, vtable, row_vec, row_alpha, row_t0, w_next, rows, T, H, flags);
-    if (rc) return rc;
-    if (!aligned16(mlp_out) || !aligned16(w_post)) return IA_ERR_ALIGN;
-    if (rows == 0) return 0;
-    K2Params p{};
-    p.h = residual; p.y = y; p.mlp = mlp_out; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
-    p.row_t0 = row_t0; p.w = w_next; p.w_post = w_post; p.eps = eps; p.inv_h = 1.0f / (float)H;
-    p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
-    // Bulk-copy staged form (MLP-output row staged, residual row through registers) where both weight rows
-    // and two one-row stages per warp fit; measured 2x the register form at 25 600 x 3584.
-    const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
-    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 4 + 1024 <= 220 * 1024;
-    if (flags & IA_IMPL_TMA) {
-        if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
-    }
-    if (tma_ok && !(flags & IA_IMPL_REGS))
-        return launch_k2_tma(p, dtype, vec_dtype, IA_NORM_GEMMA, flags, static_cast<cudaStream_t>(stream));
-    return dispatch_dtype<true>(p, dtype, vec_dtype, IA_NORM_GEMMA, flags, static_cast<cudaStream_t>(stream));
+    return ia_gemma2_tail_inject_rmsnorm_tap(mlp_out, residual, y, vtable, row_vec, row_alpha, row_t0, w_post, w_next, eps, rows,
+                                             T, H, pos0, dtype, vec_dtype, flags, nullptr, nullptr, 0, stream);
 }
 
 extern "C" int ia_add_inject_rmsnorm(void *h, const void *add, void *y, const void *vtable, const int32_t *row_vec,
                                      const float *row_alpha, const int32_t *row_t0, const void *w, float eps,
                                      int64_t rows, int64_t T, int64_t H, int32_t pos0, int32_t dtype,
                                      int32_t vec_dtype, int32_t variant, int32_t flags, void *stream) {
-    using namespace ia;
-    if (!add) return IA_ERR_NULL;
-    int rc = check_common(h, y, vtable, row_vec, row_alpha, row_t0, w, rows, T, H, flags);
-    if (rc) return rc;
-    if (!aligned16(add)) return IA_ERR_ALIGN;
-    if (variant != IA_NORM_LLAMA && variant != IA_NORM_GEMMA) return IA_ERR_DTYPE;
-    if (rows == 0) return 0;
-    K2Params p{};
-    p.h = h; p.y = y; p.mlp = nullptr; p.add = add; p.vtable = vtable; p.row_vec = row_vec; p.row_alpha = row_alpha;
-    p.row_t0 = row_t0; p.w = w; p.w_post = nullptr; p.eps = eps; p.inv_h = 1.0f / (float)H;
-    p.nvec = (int)(rows * T); p.T = (int)T; p.H = (int)H; p.pos0 = pos0; p.steer_all = (flags & IA_STEER_ALL) ? 1 : 0;
-    // the weight row and two one-row stages per warp must fit in shared memory
-    const int64_t row_bytes = H * (dtype == IA_F32 ? 4 : 2);
-    const bool tma_ok = vec_dtype == dtype && (H & 127) == 0 && row_bytes * 3 + 1024 <= 220 * 1024;
-    if (flags & IA_IMPL_TMA) {
-        if (!tma_ok) return vec_dtype != dtype ? IA_ERR_DTYPE : IA_ERR_SHAPE;
-    }
-    if (tma_ok && !(flags & IA_IMPL_REGS))
-        return launch_k2_tma(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
-    return dispatch_dtype<false>(p, dtype, vec_dtype, variant, flags, static_cast<cudaStream_t>(stream));
+    return ia_add_inject_rmsnorm_tap(h, add, y, vtable, row_vec, row_alpha, row_t0, w, eps, rows, T, H, pos0, dtype, vec_dtype,
+                                     variant, flags, nullptr, nullptr, 0, stream);
 }

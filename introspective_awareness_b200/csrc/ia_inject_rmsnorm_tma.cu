@@ -13,55 +13,11 @@
 // with batched loads instead, which halves the stage and doubles the warps (chosen per launch).
 // Outputs leave through ordinary 64-bit stores (fire-and-forget; they never stall the warp).
 
+#include <atomic>
+
 #include "ia_k2_common.cuh"
 
 namespace ia {
-
-__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(void *bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(void *bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(void *bar, unsigned parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, unsigned bytes, void *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
-                     smem_u32(smem_dst)),
-                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
-
-struct RowMeta {
-    int vi;
-    float alpha;
-    bool steer;
-};
-
-template <typename T> __device__ __forceinline__ RowMeta load_meta(const K2Params &p, int vec) {
-    RowMeta m;
-    const int row = vec / p.T;
-    const int pos = vec - row * p.T;
-    m.vi = p.row_vec ? __ldg(p.row_vec + row) : -1;
-    const int t0 = (p.row_vec && !p.steer_all) ? __ldg(p.row_t0 + row) : 0;
-    m.alpha = p.row_vec ? __ldg(p.row_alpha + row) : 0.0f;
-    m.steer = m.vi >= 0 && (p.steer_all || (pos + p.pos0 >= t0));
-    return m;
-}
 
 // S = stages per warp: one being consumed, S-1 being filled (prefetch distance S-1 vectors).
 // STAGE_V: the concept-table row is bulk-copied into the stage too (16 KB per stage at H = 4096);
@@ -220,6 +176,11 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
             for (int g = lane; g < G; g += 32) sumsq4<T>(ld4<T>(h_s + 4 * g), a0, a1, a2, a3);
         }
         const float r = rinv<IEEE>(__fmul_rn(warp_total(a0, a1, a2, a3), p.inv_h), p.eps);
+        if (cur.tap) {  // extraction capture: the updated row (it sits in the stage), compactly
+            T *cp = static_cast<T *>(p.cap_out) + (size_t)cur.row * H;
+#pragma unroll 4
+            for (int g = lane; g < G; g += 32) st4<T>(cp + 4 * g, ld4<T>(h_s + 4 * g));
+        }
 #pragma unroll 4
         for (int g = lane; g < G; g += 32) {
             Pack4<T> out;
@@ -251,14 +212,14 @@ template <typename T, int VARIANT, bool IEEE, int S, bool STAGE_V, int ADD> stat
     auto kern = k2_tma_kernel<T, VARIANT, IEEE, S, STAGE_V, ADD>;
     // opt in to large dynamic shared memory once per instantiation and device (first call = a warm-up
     // call, i.e. not under stream capture)
-    static bool configured[64] = {false};
+    static std::atomic<bool> configured[64];  // any host thread may be first on a device
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
-    if (!configured[dev]) {
+    if (!configured[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return (int)e;
-        configured[dev] = true;
+        configured[dev].store(true, std::memory_order_release);
     }
     long ctas = ((long)p.nvec + nwarps - 1) / nwarps;
     if (ctas > sms) ctas = sms;

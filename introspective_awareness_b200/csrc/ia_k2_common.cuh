@@ -24,7 +24,16 @@ struct K2Params {
     int H;
     int pos0;
     int steer_all;
+    // optional tap (the extraction capture folded into this pass): the UPDATED row of position cap_pos(row) is
+    // also written to cap_out[row, :] — cap_pos(row) = cap_tok[row] if cap_tok else cap_t
+    void *cap_out;           // [rows, H] or NULL
+    const int32_t *cap_tok;  // [rows] or NULL
+    int cap_t;
 };
+
+__device__ __forceinline__ bool tap_here(const K2Params &p, int row, int pos) {
+    return p.cap_out != nullptr && pos == (p.cap_tok ? __ldg(p.cap_tok + row) : p.cap_t);
+}
 
 template <bool IEEE> __device__ __forceinline__ float rinv(float var, float eps) {
     float t = __fadd_rn(var, eps);
@@ -153,9 +162,65 @@ __device__ __forceinline__ void norm4<__nv_bfloat16, IA_NORM_LLAMA>(const Pack4<
     out.raw.y = as_u32(__hmul2_rn(as_bf162(w.raw.y), n1));
 }
 
+// ---- mbarrier / bulk-copy (TMA) helpers shared by the staged and the streaming kernels ----------
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(void *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(void *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, unsigned bytes, void *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+
+struct RowMeta {
+    int vi;
+    float alpha;
+    bool steer;
+    bool tap;  // this vector's updated row is also written to cap_out[row]
+    int row;
+};
+
+template <typename T> __device__ __forceinline__ RowMeta load_meta(const K2Params &p, int vec) {
+    RowMeta m;
+    const int row = vec / p.T;
+    const int pos = vec - row * p.T;
+    m.vi = p.row_vec ? __ldg(p.row_vec + row) : -1;
+    const int t0 = (p.row_vec && !p.steer_all) ? __ldg(p.row_t0 + row) : 0;
+    m.alpha = p.row_vec ? __ldg(p.row_alpha + row) : 0.0f;
+    m.steer = m.vi >= 0 && (p.steer_all || (pos + p.pos0 >= t0));
+    m.row = row;
+    m.tap = tap_here(p, row, pos);
+    return m;
+}
+
+
 // Bulk-copy (TMA) staged implementation, ia_inject_rmsnorm_tma.cu.  Returns IA_ERR_DTYPE / IA_ERR_SHAPE for
 // combinations it does not cover (callers then use the register kernel).
 int launch_k2_tma(const K2Params &p, int dtype, int vec_dtype, int variant, int flags, cudaStream_t s);
+// Streaming implementation (row in registers, quarter-row landing slots), ia_inject_rmsnorm_stream.cu.
+// k2_stream_supported: does it cover this shape / dtype combination at all?
+bool k2_stream_supported(const K2Params &p, int dtype, int vec_dtype);
+int launch_k2_stream(const K2Params &p, int dtype, int vec_dtype, int variant, int flags, cudaStream_t s);
 int sm_count();
 
 }  // namespace ia

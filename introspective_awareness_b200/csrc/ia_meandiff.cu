@@ -16,6 +16,8 @@
 // HBM-bound streaming: algorithmic bytes per layer (n_concept + n_base)*H*e_in + n_out*H*e_out.
 
 #include <algorithm>
+#include <atomic>
+#include <cstdlib>
 #include <mutex>
 
 #include "ia_common.cuh"
@@ -345,6 +347,114 @@ __global__ void __launch_bounds__(128, 4) k1_fused_kernel(RowSource<T> csrc, Row
                  warp + (int64_t)nwarps * RowBatch<T>::kRows, nwarps, o);
 }
 
+// Streaming path for n_base <= 256 (or RAW): one WARP per (layer, 256-column tile, share of the concept rows).
+// A lane owns 8 columns, as everywhere in K1, and every byte it consumes it has fetched itself: each lane
+// pushes its own 16 bytes of every row of the unit — baseline rows first, then its share of the concept rows —
+// through a private ring in shared memory with cp.async (kDepth groups of kGroupRows rows in flight), adds
+// the baseline rows in row order as they land, turns the sum into the two means, and emits the concept
+// rows as they land.  No lane ever reads another lane's bytes, so there is no barrier anywhere: a warp
+// has ~16 KB of loads in flight from its first instruction to its last row, and the warps of an SM are
+// in different phases (summing / emitting / storing) at any moment instead of marching in step.
+// Splitting the concept rows of a (layer, tile) over `nsplit` warps repeats the baseline reads (L2 hits
+// after the first warp) but not the arithmetic order: every warp adds all baseline rows in row order.
+constexpr int kGroupRows = 4;
+constexpr int kDepth = 8;  // groups in flight per lane
+
+template <typename T, bool WANT_NORM>
+__global__ void __launch_bounds__(128) k1_stream_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
+                                                        int nsplit, K1Out o) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int kLaneBytes = 8 * (int)sizeof(T);             // 16 (or 32) bytes of a row per lane
+    constexpr int kRingRows = kGroupRows * kDepth;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
+    if (unit >= (int64_t)n_layers * o.ntiles * nsplit) return;
+    const int split = (int)(unit % nsplit);
+    const int tile = (int)((unit / nsplit) % o.ntiles);
+    const int layer = (int)(unit / ((int64_t)nsplit * o.ntiles));
+    const int col = tile * kTileCols + lane * 8;
+    const bool active = col < H;
+    // ring[row slot][lane]: lane-private 16/32-byte cells
+    unsigned char *ring = smem + ((size_t)warp * kRingRows * 32 + lane) * kLaneBytes;
+    const int64_t nb = raw ? 0 : bsrc.n;
+    const int64_t n_mine = csrc.n > split ? (csrc.n - split + nsplit - 1) / nsplit : 0;
+    const int64_t total = nb + n_mine;
+    const int64_t ngroups = (total + kGroupRows - 1) / kGroupRows;
+
+    auto issue_group = [&](int64_t g) {
+        if (active && g < ngroups) {
+#pragma unroll
+            for (int u = 0; u < kGroupRows; ++u) {
+                const int64_t q = g * kGroupRows + u;
+                if (q < total) {
+                    const T *src = q < nb ? bsrc.at(layer, q, H) : csrc.at(layer, split + (q - nb) * nsplit, H);
+                    unsigned char *d = ring + (size_t)((g % kDepth) * kGroupRows + u) * 32 * kLaneBytes;
+                    cp_async16(d, src + col);
+                    if (sizeof(T) == 4) cp_async16(d + 16, src + col + 4);
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::);  // always: the group count per iteration stays fixed
+    };
+#pragma unroll
+    for (int g = 0; g < kDepth; ++g) issue_group(g);
+
+    float acc[8], mean32[8], meanr[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { acc[i] = 0.f; mean32[i] = 0.f; meanr[i] = 0.f; }
+    bool have_mean = nb == 0;
+    for (int64_t g = 0; g < ngroups; ++g) {
+        asm volatile("cp.async.wait_group %0;\n" ::"n"(kDepth - 1) : "memory");  // group g has landed
+#pragma unroll
+        for (int u = 0; u < kGroupRows; ++u) {
+            const int64_t q = g * kGroupRows + u;
+            if (q >= total) break;
+            float a[8];
+            if (active) {
+                lds8<T>(ring + (size_t)((g % kDepth) * kGroupRows + u) * 32 * kLaneBytes, a);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) a[i] = 0.f;
+            }
+            if (q < nb) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], a[i]);
+                continue;
+            }
+            if (!have_mean) {
+                const float n = (float)nb;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    mean32[i] = active ? __fdiv_rn(acc[i], n) : 0.f;
+                    meanr[i] = Elt<T>::rd(mean32[i]);
+                }
+                have_mean = true;
+            }
+            const int64_t c = split + (q - nb) * nsplit;
+            float v32[8], vr[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                v32[i] = raw ? a[i] : __fsub_rn(a[i], mean32[i]);
+                vr[i] = raw ? a[i] : Elt<T>::rd(__fsub_rn(a[i], meanr[i]));
+            }
+            const int64_t orow = (int64_t)layer * csrc.n + c;
+            if (active) {
+                if (o.out_f32) store8<float>(o.out_f32 + orow * H + col, v32);
+                store8<T>(static_cast<T *>(o.out_rounded) + orow * H + col, vr);
+            }
+            if (WANT_NORM) {
+                const float p32 = sq8_warp(v32);
+                const float pr = sq8_warp(vr);
+                if (lane == 0) {
+                    o.part32[orow * o.ntiles + tile] = p32;
+                    o.partr[orow * o.ntiles + tile] = pr;
+                }
+            }
+        }
+        issue_group(g + kDepth);  // refills the cells this lane has just read
+    }
+}
+
 // Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.  Small CTAs
 // (4 warps, 32 KB of staging) so that ~7 are resident per SM: a CTA's start-up and drain (pointer
 // table -> first rows -> last adds -> store), during which it has no loads in flight, is then
@@ -499,6 +609,19 @@ __global__ void __launch_bounds__(128) k1_norm_kernel(int64_t n_rows, int H, int
 // host side
 // ---------------------------------------------------------------------------------------------
 
+// cudaFuncSetAttribute once per kernel and device (the first call on a device is a set-up call: make it
+// outside any stream capture).
+template <typename K> static int opt_in_smem(K kern, std::atomic<bool> (&done)[64], int bytes) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (!done[dev].load(std::memory_order_acquire)) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e != cudaSuccess) return (int)e;
+        done[dev].store(true, std::memory_order_release);
+    }
+    return 0;
+}
+
 static inline int64_t up64(int64_t x) { return (x + 63) / 64 * 64; }  // floats -> 256-byte multiples
 static inline int nchunks_of(int64_t n) { return (int)((n + kChunkRows - 1) / kChunkRows); }
 
@@ -534,8 +657,9 @@ static int run_segsum(const RowSource<T> &src, int L, int H, float *part, float 
     if (nch > 1) {
         const int64_t per = (int64_t)L * H;
         const int cr_smem = kCrPass * kCrCols * (int)sizeof(float);
-        e = cudaFuncSetAttribute(k1_chunk_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cr_smem);
-        if (e != cudaSuccess) return (int)e;
+        static std::atomic<bool> cr_done[64];
+        const int rc = opt_in_smem(k1_chunk_reduce_kernel, cr_done, cr_smem);
+        if (rc) return rc;
         k1_chunk_reduce_kernel<<<(unsigned)((per + kCrCols - 1) / kCrCols), 256, cr_smem, s>>>(part, sum_out, per, nch);
         e = cudaGetLastError();
     }
@@ -563,29 +687,53 @@ static int run_finalize(const RowSource<T> &csrc, const float *base_sum, int64_t
 }
 
 template <typename T>
-static int gather_meandiff_t(const void *const *cptrs, int64_t Tc, const int32_t *crow, const int32_t *ctok, int64_t nc,
-                             const void *const *bptrs, int64_t Tb, const int32_t *brow, const int32_t *btok, int64_t nb,
-                             int L, int H, int mode, int normalize, float *out_f32, void *out_rounded, float *out_norm,
-                             float *ws, cudaStream_t s) {
+static int meandiff_t(const RowSource<T> &csrc, const RowSource<T> &bsrc, int L, int H, int mode, int normalize, float *out_f32,
+                      void *out_rounded, float *out_norm, float *ws, cudaStream_t s) {
+    const int64_t nc = csrc.n, nb = bsrc.n;
     const WsLayout wl = ws_layout(L, nc, nb, H, mode);
     const int ntiles = (H + kTileCols - 1) / kTileCols;
-    RowSource<T> csrc{cptrs, nullptr, crow, ctok, Tc, nc};
-    RowSource<T> bsrc{bptrs, nullptr, brow, btok, Tb, nb};
     K1Out o{out_f32, out_rounded, ws + wl.part32, ws + wl.partr, ntiles};
     const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : nc;
     if (mode != IA_MODE_POSNEG && (mode == IA_MODE_RAW || nb <= kChunkRows)) {
-        // all baseline rows in one pass when they fit half the staging budget each way (two halves of
-        // `stage_rows` rows), otherwise two alternating half-size passes
-        const int row_bytes = kTileCols * (int)sizeof(T);
-        const int half_rows = kStageBytes / 2 / row_bytes;
-        const int stage_rows = nb <= 2 * half_rows ? (int)std::max<int64_t>(nb, 1) : half_rows;
-        const int smem = kMeanBytes + (mode == IA_MODE_RAW ? 0 : (nb <= 2 * half_rows ? stage_rows : 2 * stage_rows) * row_bytes);
-        cudaError_t e = cudaFuncSetAttribute(k1_fused_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMeanBytes + kStageBytes);
+        const bool want_norm = normalize || out_norm;
+        static const bool use_cta_kernel = std::getenv("IA_K1_CTA") != nullptr;  // A/B switch for tools/kbench.py
+        cudaError_t e;
+        if (!use_cta_kernel) {
+            // streaming kernel: enough warps to fill the machine (~10 per SM), each a (layer, tile, share of
+            // the concept rows) unit
+            const int64_t units = (int64_t)L * ntiles;
+            int nsplit = (int)std::min<int64_t>(std::max<int64_t>(1, (148 * 10 + units - 1) / units), std::max<int64_t>(1, std::min<int64_t>(nc, 8)));
+            const int lane_bytes = 8 * (int)sizeof(T);
+            const int smem = 4 * kGroupRows * kDepth * 32 * lane_bytes;
+            const int64_t warps = units * nsplit;
+            int rc;
+            if (want_norm) {
+                static std::atomic<bool> done[64];
+                rc = opt_in_smem(k1_stream_kernel<T, true>, done, smem);
+                if (rc) return rc;
+                k1_stream_kernel<T, true><<<(unsigned)((warps + 3) / 4), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, nsplit, o);
+            } else {
+                static std::atomic<bool> done[64];
+                rc = opt_in_smem(k1_stream_kernel<T, false>, done, smem);
+                if (rc) return rc;
+                k1_stream_kernel<T, false><<<(unsigned)((warps + 3) / 4), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, nsplit, o);
+            }
+            e = cudaGetLastError();
+        } else {
+            // all baseline rows in one pass when they fit half the staging budget each way (two halves of
+            // `stage_rows` rows), otherwise two alternating half-size passes
+            const int row_bytes = kTileCols * (int)sizeof(T);
+            const int half_rows = kStageBytes / 2 / row_bytes;
+            const int stage_rows = nb <= 2 * half_rows ? (int)std::max<int64_t>(nb, 1) : half_rows;
+            const int smem = kMeanBytes + (mode == IA_MODE_RAW ? 0 : (nb <= 2 * half_rows ? stage_rows : 2 * stage_rows) * row_bytes);
+            static std::atomic<bool> done[64];
+            const int rc = opt_in_smem(k1_fused_kernel<T>, done, kMeanBytes + kStageBytes);
+            if (rc) return rc;
+            k1_fused_kernel<T><<<(unsigned)(L * ntiles), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, o);
+            e = cudaGetLastError();
+        }
         if (e != cudaSuccess) return (int)e;
-        k1_fused_kernel<T><<<(unsigned)(L * ntiles), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, o);
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return (int)e;
-        if (!normalize && !out_norm) return 0;  // nobody reads the norms: the partials stay in the workspace
+        if (!want_norm) return 0;  // nobody reads the norms
         const int64_t rows = (int64_t)L * n_out;
         k1_norm_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(rows, H, normalize, out_norm, o);
         return (int)cudaGetLastError();
@@ -597,6 +745,24 @@ static int gather_meandiff_t(const void *const *cptrs, int64_t Tc, const int32_t
         if (rc) return rc;
     }
     return run_finalize<T>(csrc, ws + wl.base_sum, nb, ws + wl.pos_sum, nc, L, H, mode, normalize, out_norm, o, s);
+}
+
+template <typename T>
+static int gather_meandiff_t(const void *const *cptrs, int64_t Tc, const int32_t *crow, const int32_t *ctok, int64_t nc,
+                             const void *const *bptrs, int64_t Tb, const int32_t *brow, const int32_t *btok, int64_t nb,
+                             int L, int H, int mode, int normalize, float *out_f32, void *out_rounded, float *out_norm,
+                             float *ws, cudaStream_t s) {
+    RowSource<T> csrc{cptrs, nullptr, crow, ctok, Tc, nc};
+    RowSource<T> bsrc{bptrs, nullptr, brow, btok, Tb, nb};
+    return meandiff_t<T>(csrc, bsrc, L, H, mode, normalize, out_f32, out_rounded, out_norm, ws, s);
+}
+
+template <typename T>
+static int compact_meandiff_t(const void *cacts, int64_t nc, const void *bacts, int64_t nb, int L, int H, int mode, int normalize,
+                              float *out_f32, void *out_rounded, float *out_norm, float *ws, cudaStream_t s) {
+    RowSource<T> csrc{nullptr, static_cast<const T *>(cacts), nullptr, nullptr, 1, nc};
+    RowSource<T> bsrc{nullptr, static_cast<const T *>(bacts), nullptr, nullptr, 1, nb};
+    return meandiff_t<T>(csrc, bsrc, L, H, mode, normalize, out_f32, out_rounded, out_norm, ws, s);
 }
 
 static int check_sizes(int64_t L, int64_t H, int64_t n) {
@@ -646,6 +812,40 @@ extern "C" int ia_gather_meandiff(const void *const *concept_ptrs, int64_t Tc, c
     }
 }
 
+extern "C" int ia_meandiff_compact(const void *concept_acts, int64_t n_concept, const void *base_acts, int64_t n_base,
+                                   int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,
+                                   void *out_rounded, float *out_norm, void *workspace, int64_t workspace_bytes,
+                                   int32_t dtype, void *stream) {
+    using namespace ia;
+    if (mode < IA_MODE_BASELINE || mode > IA_MODE_POSNEG) return IA_ERR_DTYPE;
+    if (!concept_acts || !out_rounded || !workspace) return IA_ERR_NULL;
+    if (mode != IA_MODE_RAW && !base_acts) return IA_ERR_NULL;
+    int rc = check_sizes(n_layers, H, n_concept);
+    if (rc) return rc;
+    if ((mode != IA_MODE_RAW && n_base < 1) || n_base < 0) return IA_ERR_SHAPE;
+    if (!aligned16(concept_acts) || (base_acts && !aligned16(base_acts)) || !aligned16(out_rounded) || !aligned16(workspace) ||
+        (out_f32 && !aligned16(out_f32)))
+        return IA_ERR_ALIGN;
+    if (mode == IA_MODE_RAW) n_base = 0;
+    if (workspace_bytes < ia_meandiff_workspace_bytes(n_layers, n_concept, n_base, H, mode)) return IA_ERR_WORKSPACE;
+    if (n_concept == 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    float *ws = static_cast<float *>(workspace);
+    switch (dtype) {
+    case IA_BF16:
+        return compact_meandiff_t<__nv_bfloat16>(concept_acts, n_concept, base_acts, n_base, (int)n_layers, (int)H, mode, normalize,
+                                                 out_f32, out_rounded, out_norm, ws, s);
+    case IA_F16:
+        return compact_meandiff_t<__half>(concept_acts, n_concept, base_acts, n_base, (int)n_layers, (int)H, mode, normalize, out_f32,
+                                          out_rounded, out_norm, ws, s);
+    case IA_F32:
+        return compact_meandiff_t<float>(concept_acts, n_concept, base_acts, n_base, (int)n_layers, (int)H, mode, normalize, out_f32,
+                                         out_rounded, out_norm, ws, s);
+    default:
+        return IA_ERR_DTYPE;
+    }
+}
+
 extern "C" int ia_gather_segsum(const void *const *layer_ptrs, int64_t T, const int32_t *row_idx, const int32_t *tok_idx,
                                 int64_t n_rows, int64_t n_layers, int64_t H, void *out_rows, float *out_sum, void *workspace,
                                 int64_t workspace_bytes, int32_t dtype, void *stream) {
@@ -671,6 +871,35 @@ extern "C" int ia_gather_segsum(const void *const *layer_ptrs, int64_t T, const 
     case IA_F32: {
         RowSource<float> src{layer_ptrs, nullptr, row_idx, tok_idx, T, n_rows};
         return run_segsum<float>(src, (int)n_layers, (int)H, part, out_sum, static_cast<float *>(out_rows), s);
+    }
+    default:
+        return IA_ERR_DTYPE;
+    }
+}
+
+extern "C" int ia_segsum_compact(const void *rows, int64_t n_rows, int64_t n_layers, int64_t H, float *out_sum, void *workspace,
+                                 int64_t workspace_bytes, int32_t dtype, void *stream) {
+    using namespace ia;
+    if (!rows || !out_sum || !workspace) return IA_ERR_NULL;
+    int rc = check_sizes(n_layers, H, n_rows);
+    if (rc) return rc;
+    if (!aligned16(rows) || !aligned16(out_sum) || !aligned16(workspace)) return IA_ERR_ALIGN;
+    if (workspace_bytes < ia_meandiff_workspace_bytes(n_layers, 0, n_rows, H, IA_MODE_BASELINE)) return IA_ERR_WORKSPACE;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const WsLayout wl = ws_layout(n_layers, 0, n_rows, H, IA_MODE_BASELINE);
+    float *part = static_cast<float *>(workspace) + wl.base_part;
+    switch (dtype) {
+    case IA_BF16: {
+        RowSource<__nv_bfloat16> src{nullptr, static_cast<const __nv_bfloat16 *>(rows), nullptr, nullptr, 1, n_rows};
+        return run_segsum<__nv_bfloat16>(src, (int)n_layers, (int)H, part, out_sum, nullptr, s);
+    }
+    case IA_F16: {
+        RowSource<__half> src{nullptr, static_cast<const __half *>(rows), nullptr, nullptr, 1, n_rows};
+        return run_segsum<__half>(src, (int)n_layers, (int)H, part, out_sum, nullptr, s);
+    }
+    case IA_F32: {
+        RowSource<float> src{nullptr, static_cast<const float *>(rows), nullptr, nullptr, 1, n_rows};
+        return run_segsum<float>(src, (int)n_layers, (int)H, part, out_sum, nullptr, s);
     }
     default:
         return IA_ERR_DTYPE;

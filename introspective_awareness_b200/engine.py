@@ -171,8 +171,9 @@ class StaticKV:
 class DecoderEngine:
     """Layer loop over a Hugging Face Llama / Qwen2 / Gemma-2 causal LM."""
 
-    def __init__(self, model, fuse_gemma_tail: bool = True, attention: str = "hf", fused_norms: Optional[bool] = None):
-        """attention: "hf" keeps the model's own attention function; "gqa" (= "auto") swaps in
+    def __init__(self, model, fuse_gemma_tail: bool = True, attention: str = "auto", fused_norms: Optional[bool] = None):
+        """attention: "hf" keeps the model's own attention function; "gqa" (= "auto" on a CUDA device; on the CPU
+        "auto" means "hf") swaps in
         `_gqa_sdpa_forward`, which never materialises K/V per query head (HF's `repeat_kv`): torch's
         grouped-query kernel where head_dim <= 128 (measured 3.2x faster decode on Llama-3.1-8B), the folded form
         `_gqa_folded` above that (Gemma-2's 256: 1.9x faster bench step).  Both are bit-identical to the reference
@@ -210,6 +211,9 @@ class DecoderEngine:
         self.counters = {"k2_launches": 0, "k1_launches": 0, "rope_launches": 0, "act_launches": 0}
         self.fused_norms = (self.device.type == "cuda") if fused_norms is None else fused_norms
         self.graph_extraction = True
+        # position ids of the extraction forwards: "arange" = the reference's (no position_ids passed, so a
+        # left-padded row is numbered from its pad count); "mask" = pad-aware, as generation numbers them
+        self.extraction_positions = "arange"
         self.additive_masks = True   # convert boolean attention masks once per forward, not once per layer
         # rotary embedding: one fused launch (same rounding points) instead of HF's ~8 eager kernels
         import sys as _sys
@@ -217,7 +221,7 @@ class DecoderEngine:
         self.fused_rope = self.device.type == "cuda"
         self._extract_graphs: Dict[tuple, tuple] = {}
         if attention == "auto":
-            attention = "gqa"
+            attention = "gqa" if self.device.type == "cuda" else "hf"
         self.attention = attention
         if attention == "gqa":
             _register_attention()
@@ -339,15 +343,18 @@ class DecoderEngine:
 
     def _run_layers(self, h: torch.Tensor, pos_emb, masks, cache, steer: Optional[SteerSpec] = None,
                     pos0: int = 0, decode: bool = False, stop_after: Optional[int] = None,
-                    capture: Optional[Sequence[int]] = None):
-        """Runs decoder layers on h [B,T,H].  Returns (final_normed_or_None, captured dict).
-        With `stop_after` the loop ends after that layer and nothing is normed."""
+                    capture: Optional[Dict[int, torch.Tensor]] = None, cap_t: int = -1):
+        """Runs decoder layers on h [B,T,H].  Returns (final_normed_or_None, capture).
+        With `stop_after` the loop ends after that layer and nothing is normed.
+        capture: {layer index: [B, H] buffer}; the residual stream after that layer at position `cap_t` of every
+        row is written into the buffer (reference model_utils.py:312-321: the hook's slice of the layer output) —
+        by the K2 launch that finishes the layer where there is one (its tap output), by a row slice otherwise."""
         if self.native_block and h.is_cuda and self.fused_norms:
-            return self._run_layers_native(h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture)
+            return self._run_layers_native(h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture, cap_t)
         if self.is_gemma2 and self.fuse_gemma_tail and self.gemma_tail_everywhere and h.is_cuda and self.fused_norms:
-            return self._run_layers_gemma(h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture)
-        captured: Dict[int, torch.Tensor] = {}
-        want = set(capture or ())
+            return self._run_layers_gemma(h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture, cap_t)
+        captured = capture or {}
+        want = set(captured)
         last = self.n_layers - 1 if stop_after is None else stop_after
         normed_in = None  # y from K2 = already-normed input of the next layer
         final = None
@@ -384,7 +391,7 @@ class DecoderEngine:
                     else:
                         final = y
                     if i in want:
-                        captured[i] = h
+                        captured[i].copy_(h[:, cap_t])
                     continue
                 h = residual + self.norm(layer.post_feedforward_layernorm, m)
             else:
@@ -412,7 +419,7 @@ class DecoderEngine:
                 else:
                     final = y
             if i in want:
-                captured[i] = h
+                captured[i].copy_(h[:, cap_t])
         if stop_after is None and final is None:
             final = self.norm(self.inner.norm, h)
         return final, captured
@@ -489,24 +496,25 @@ class DecoderEngine:
         return mlp.down_proj(kernels.silu_mul(g, u))
 
     def _k2(self, h, weight, add=None, steer: Optional[SteerSpec] = None, pos0: int = 0, decode: bool = False,
-            timed: bool = False):
+            timed: bool = False, cap_out: Optional[torch.Tensor] = None, cap_t: int = -1):
         ev = None
         if timed and self.k2_events is not None and not decode:
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record()
         if steer is None:
-            y = kernels.inject_rmsnorm(h, weight, self.eps, self.variant, add=add)
+            y = kernels.inject_rmsnorm(h, weight, self.eps, self.variant, add=add, cap_out=cap_out, cap_t=cap_t)
         else:
             y = kernels.inject_rmsnorm(h, weight, self.eps, self.variant, vtable=steer.vtable, row_vec=steer.row_vec,
                                        row_alpha=steer.row_alpha, row_t0=None if decode else steer.row_t0, pos0=pos0,
-                                       steer_all=decode or steer.row_t0 is None, add=add)
+                                       steer_all=decode or steer.row_t0 is None, add=add, cap_out=cap_out, cap_t=cap_t)
         if ev is not None:
             ev[1].record()
             self.k2_events.append((ev[0], ev[1], h.numel() * h.element_size()))
         self.counters["k2_launches"] += 1
         return y
 
-    def _gemma_tail(self, branch, h, w_post, w_next, steer=None, pos0=0, decode=False, timed=False):
+    def _gemma_tail(self, branch, h, w_post, w_next, steer=None, pos0=0, decode=False, timed=False, cap_out=None,
+                    cap_t: int = -1):
         """h <- h + gemma_norm(branch; w_post) [+ alpha*v]; returns gemma_norm(h; w_next).  One launch for what the
         HF layer does as norm kernel + add kernel (+ hook) + the next norm."""
         ev = None
@@ -518,20 +526,19 @@ class DecoderEngine:
             kw = dict(vtable=steer.vtable, row_vec=steer.row_vec, row_alpha=steer.row_alpha,
                       row_t0=None if decode else steer.row_t0, pos0=pos0, steer_all=decode or steer.row_t0 is None)
         y = kernels.gemma2_tail_inject_rmsnorm(branch if branch.is_contiguous() else branch.contiguous(), h, w_post, w_next,
-                                               self.eps, **kw)
+                                               self.eps, cap_out=cap_out, cap_t=cap_t, **kw)
         if ev is not None:
             ev[1].record()
             self.k2_events.append((ev[0], ev[1], h.numel() * h.element_size()))
         self.counters["k2_launches"] += 1
         return y
 
-    def _run_layers_gemma(self, h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture):
+    def _run_layers_gemma(self, h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture, cap_t=-1):
         """Gemma-2 with the block-tail form of K2 at BOTH residual joins of every layer (after attention:
         post_attention_layernorm + add + pre_feedforward_layernorm; after the MLP: post_feedforward_layernorm + add
         [+ injection] + the next layer's input_layernorm).  Attention and MLP stay the HF modules.  The residual
         stream is one buffer updated in place."""
-        captured: Dict[int, torch.Tensor] = {}
-        want = set(capture or ())
+        captured = capture or {}
         last = self.n_layers - 1 if stop_after is None else stop_after
         if not h.is_contiguous():
             h = h.contiguous()
@@ -545,21 +552,24 @@ class DecoderEngine:
             m = layer.mlp(x)
             st = steer if (steer is not None and steer.layer_idx == i) else None
             nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
+            if i == last and stop_after is not None and st is None and i in captured:
+                # nothing downstream: finish the captured rows only (B vectors instead of B*T), in the capture buffer
+                rows = captured[i]
+                rows.copy_(h[:, cap_t])
+                self._gemma_tail(m[:, cap_t].unsqueeze(1), rows.unsqueeze(1), layer.post_feedforward_layernorm.weight, nxt.weight)
+                break
             y = self._gemma_tail(m, h, layer.post_feedforward_layernorm.weight, nxt.weight, steer=st, pos0=pos0,
-                                 decode=decode, timed=st is not None)
+                                 decode=decode, timed=st is not None, cap_out=captured.get(i), cap_t=cap_t)
             if i < last:
                 x = y
             elif stop_after is None:
                 final = y
-            if i in want:
-                captured[i] = h if i == last else h.clone()
         return final, captured
 
-    def _run_layers_native(self, h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture):
+    def _run_layers_native(self, h, pos_emb, masks, cache, steer, pos0, decode, stop_after, capture, cap_t=-1):
         """Same contract as `_run_layers`.  The residual stream `h` is ONE buffer updated in place by K2
         (h <- h + branch [+ alpha*v]); K2's second output is the next sub-block's normed input."""
-        captured: Dict[int, torch.Tensor] = {}
-        want = set(capture or ())
+        captured = capture or {}
         last = self.n_layers - 1 if stop_after is None else stop_after
         if not h.is_contiguous():
             h = h.contiguous()
@@ -572,16 +582,19 @@ class DecoderEngine:
             m = self._mlp_native(layer, i, x)
             st = steer if (steer is not None and steer.layer_idx == i) else None
             if i == last and stop_after is not None and st is None:
-                h.add_(m)  # nothing reads a normed output after the last requested layer
+                # nothing reads a normed output after the last requested layer: finish the captured rows only
+                if i in captured:
+                    torch.add(h[:, cap_t], m[:, cap_t], out=captured[i])
+                else:
+                    h.add_(m)
             else:
                 nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
-                y = self._k2(h, nxt.weight, add=m, steer=st, pos0=pos0, decode=decode, timed=st is not None)
+                y = self._k2(h, nxt.weight, add=m, steer=st, pos0=pos0, decode=decode, timed=st is not None,
+                             cap_out=captured.get(i), cap_t=cap_t)
                 if i < last:
                     x = y
                 elif stop_after is None:
                     final = y
-            if i in want:
-                captured[i] = h if i == last else h.clone()
         return final, captured
 
     def logits(self, normed_last: torch.Tensor) -> torch.Tensor:
@@ -593,37 +606,52 @@ class DecoderEngine:
 
     # -- extraction ---------------------------------------------------------------------------
     @torch.inference_mode()
-    def capture_layers(self, input_ids: torch.Tensor, attention_mask: torch.Tensor,
-                       layer_indices: Sequence[int], slot: int = 0) -> List[torch.Tensor]:
-        """One forward, stopped after the deepest requested layer; returns the residual stream
-        [B,T,H] after each requested layer (reference model_utils.py:312-338 runs the whole model,
-        once per layer)."""
+    def capture_rows(self, input_ids: torch.Tensor, attention_mask: torch.Tensor, layer_indices: Sequence[int],
+                     token_idx: int = -1, slot: int = 0) -> torch.Tensor:
+        """One forward, stopped after the deepest requested layer; returns the residual stream after each requested
+        layer at position `token_idx` of every row, compactly: [n_layers, B, H] in the model dtype, on the device
+        (reference model_utils.py:312-338 runs the whole model once per layer, slices the hooked layer output and
+        ships it to the host).  On the kernel paths the rows are written by the K2 launch that finishes the layer
+        (its tap output): no copy of the residual stream is kept and nothing re-reads it."""
         layer_indices = [int(i) for i in layer_indices]
         for i in layer_indices:
             if not 0 <= i < self.n_layers:
                 raise IndexError(f"layer {i} out of range")
+        t_len = input_ids.shape[1]
+        cap_t = token_idx if token_idx >= 0 else t_len + token_idx  # the reference slices the padded tensor
+        if not 0 <= cap_t < t_len:
+            raise IndexError(f"token_idx {token_idx} out of range for width {t_len}")
         padded = not bool(attention_mask.all())
         # small (launch-bound) forwards replay as a CUDA graph; large ones are GPU-bound anyway and a
         # graph would pin their activations in a private pool
         if self.device.type == "cuda" and self.graph_extraction and input_ids.numel() <= 16384:
-            return self._capture_layers_graphed(input_ids, attention_mask, layer_indices, padded, slot)
-        return self._capture_layers_eager(input_ids.to(self.device), attention_mask.to(self.device), layer_indices, padded)
+            return self._capture_rows_graphed(input_ids, attention_mask, layer_indices, padded, cap_t, slot)
+        return self._capture_rows_eager(input_ids.to(self.device), attention_mask.to(self.device), layer_indices, padded, cap_t)
 
-    def _capture_layers_eager(self, ids, mask, layer_indices, padded):
+    def _capture_rows_eager(self, ids, mask, layer_indices, padded, cap_t):
         h = self.inner.embed_tokens(ids)
-        pos = self.position_ids(mask)
+        if self.extraction_positions == "arange":
+            # what the reference's forward sees: `model(**inputs)` passes no position_ids (model_utils.py:338), so
+            # Hugging Face numbers the PADDED sequence 0..T-1 and a left-padded row's positions start at its pad count
+            pos = torch.arange(ids.shape[1], device=ids.device)[None].expand(ids.shape[0], -1)
+        else:
+            pos = self.position_ids(mask)
         pos_emb = self.inner.rotary_emb(h, pos)
-        _, got = self.run_layers(h, pos_emb, self.prefill_masks(mask, padded), None, stop_after=max(layer_indices),
-                                 capture=layer_indices)
-        return [got[i] for i in layer_indices]
+        uniq = sorted(set(layer_indices))
+        buf = torch.empty((len(uniq), ids.shape[0], self.hidden), dtype=h.dtype, device=h.device)
+        self.run_layers(h, pos_emb, self.prefill_masks(mask, padded), None, stop_after=uniq[-1],
+                        capture={layer: buf[k] for k, layer in enumerate(uniq)}, cap_t=cap_t)
+        if uniq == layer_indices:
+            return buf
+        return buf[[uniq.index(i) for i in layer_indices]]
 
-    def _capture_layers_graphed(self, input_ids, attention_mask, layer_indices, padded, slot):
+    def _capture_rows_graphed(self, input_ids, attention_mask, layer_indices, padded, cap_t, slot):
         """The extraction forward is ~1500 small launches (short prompts), i.e. CPU-launch-bound when
         run eagerly: replay it as one CUDA graph per (batch, width, layers) shape.  The returned
-        tensors live in the graph's pool and are overwritten by the next replay of the same shape and
+        tensor lives in the graph's pool and is overwritten by the next replay of the same shape and
         `slot` (callers that need two captures alive at once, e.g. concept and baseline batches, use
         different slots)."""
-        key = (tuple(input_ids.shape), tuple(layer_indices), padded, slot)
+        key = (tuple(input_ids.shape), tuple(layer_indices), padded, cap_t, slot, self.extraction_positions)
         entry = self._extract_graphs.get(key)
         if entry is None:
             if len(self._extract_graphs) >= 8:
@@ -636,50 +664,42 @@ class DecoderEngine:
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 for _ in range(2):
-                    self._capture_layers_eager(ids_s, mask_s, layer_indices, padded)
+                    self._capture_rows_eager(ids_s, mask_s, layer_indices, padded, cap_t)
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             before = dict(self.counters)
             with _no_gc_during_capture(), torch.cuda.graph(g):
-                outs = self._capture_layers_eager(ids_s, mask_s, layer_indices, padded)
+                out = self._capture_rows_eager(ids_s, mask_s, layer_indices, padded, cap_t)
             g.ia_launches = {k: self.counters[k] - before[k] for k in before}
             for k in before:
                 self.counters[k] = before[k]
-            entry = (g, ids_s, mask_s, outs)
+            entry = (g, ids_s, mask_s, out)
             self._extract_graphs[key] = entry
-        g, ids_s, mask_s, outs = entry
+        g, ids_s, mask_s, out = entry
         ids_s.copy_(input_ids, non_blocking=True)
         mask_s.copy_(attention_mask, non_blocking=True)
         g.replay()
         for k, v in g.ia_launches.items():
             self.counters[k] += v
-        return outs
+        return out
 
     @torch.inference_mode()
     def extract_vectors(self, concept_ids, concept_mask, base_ids, base_mask, layer_indices: Sequence[int],
                         mode: str = "baseline", normalize: bool = False, token_idx: int = -1, want_f32: bool = True,
                         want_norm: bool = True):
         """K1 over any number of layers: two forwards (concept batch, baseline batch — the
-        reference also runs them separately, vector_utils.py:524-540) and one fused
-        gather + mean-diff + norm launch.  Returns (v_f32, v_rounded, norm) on the device,
-        each [n_layers, n_out, H] / [n_layers, n_out]."""
+        reference also runs them separately, vector_utils.py:524-540), each leaving its captured rows
+        compactly in HBM through K2's tap, and one mean-diff (+ norm) launch over them.  Returns
+        (v_f32, v_rounded, norm) on the device, each [n_layers, n_out, H] / [n_layers, n_out]."""
         if not self.device.type == "cuda":
             raise RuntimeError("concept-vector extraction needs the CUDA kernels; there is no CPU path")
-        cl = self.capture_layers(concept_ids, concept_mask, layer_indices, slot=0)
-        bl = None
+        crows = self.capture_rows(concept_ids, concept_mask, layer_indices, token_idx, slot=0)
+        brows = None
         if mode not in ("no_baseline", "raw"):
-            bl = self.capture_layers(base_ids, base_mask, layer_indices, slot=1)
-
-        def tok(t_len, n):
-            t = token_idx if token_idx >= 0 else t_len + token_idx  # reference slices the padded tensor
-            return torch.full((n,), t, dtype=torch.int32)
-
-        out = kernels.gather_meandiff(
-            cl, bl, mode, normalize, concept_tok=tok(cl[0].shape[1], cl[0].shape[0]),
-            base_tok=None if bl is None else tok(bl[0].shape[1], bl[0].shape[0]), want_f32=want_f32,
-            want_norm=want_norm)
-        self.counters["k1_launches"] += 2 if (want_norm or normalize) else 1  # fused kernel (+ norm pass)
+            brows = self.capture_rows(base_ids, base_mask, layer_indices, token_idx, slot=1)
+        out = kernels.meandiff_compact(crows, brows, mode, normalize, want_f32=want_f32, want_norm=want_norm)
+        self.counters["k1_launches"] += 2 if (want_norm or normalize) else 1  # mean-diff kernel (+ norm pass)
         return out
 
     # -- generation ---------------------------------------------------------------------------
@@ -719,9 +739,33 @@ class Session:
         self.graphs: Dict[Tuple, List] = {}
         self.pool = None
         self.step_logits: List[torch.Tensor] = []
+        # every token a row has seen (prompt incl. pads, then generated), for the repetition penalty; slots not yet
+        # written repeat column 0, which is part of the history anyway, so penalising over the whole buffer is exact
+        self.hist: Optional[torch.Tensor] = None
+        self._hist_buf: Optional[torch.Tensor] = None
+        self._eos_ids: Dict[tuple, torch.Tensor] = {}
+
+    def _eos_tensor(self, eos: Optional[tuple]) -> Optional[torch.Tensor]:
+        if not eos:
+            return None
+        t = self._eos_ids.get(eos)
+        if t is None:
+            t = torch.tensor(list(eos), dtype=torch.long, device=self.eng.device)
+            self._eos_ids[eos] = t
+        return t
+
+    def _penalise(self, lg: torch.Tensor, penalty: float) -> torch.Tensor:
+        """HF RepetitionPenaltyLogitsProcessor over the row's whole history: a seen token's logit is divided by the
+        penalty when positive and multiplied by it when negative (applies to greedy decoding too)."""
+        if penalty == 1.0:
+            return lg
+        seen = lg.gather(1, self.hist)
+        seen = torch.where(seen < 0, seen * penalty, seen / penalty)
+        return lg.scatter(1, self.hist, seen)
 
     # one cached decode step: feeds self.tok at cache position T+s-1, leaves next token in self.tok
-    def _step(self, s: int, steer: Optional[SteerSpec], greedy: bool, eos: Optional[int], pad: int):
+    def _step(self, s: int, steer: Optional[SteerSpec], greedy: bool, eos: Optional[tuple], pad: int,
+              penalty: float = 1.0):
         eng = self.eng
         eng_cache = self.cache
         eng_cache.pos = self.T + s - 1
@@ -739,18 +783,23 @@ class Session:
         if self.logits_buf is not None:
             self.logits_buf.copy_(lg)
         if greedy:
-            nxt = lg.argmax(dim=-1)
+            nxt = self._penalise(lg, penalty).argmax(dim=-1)
             self._commit(nxt, s, eos, pad)
 
-    def _commit(self, nxt: torch.Tensor, s: int, eos: Optional[int], pad: int):
-        if eos is not None:
+    def _commit(self, nxt: torch.Tensor, s: int, eos: Optional[tuple], pad: int):
+        """A finished row emits the pad token from then on; a row finishes on ANY id of the model's EOS set, as HF
+        `generate` does (Llama-3.x-Instruct lists three ids and ends a turn with the last of them)."""
+        eos_t = self._eos_tensor(eos)
+        if eos_t is not None:
             nxt = torch.where(self.unfinished, nxt, torch.full_like(nxt, pad))
-            self.unfinished &= nxt != eos
+            self.unfinished &= ~torch.isin(nxt, eos_t)
         self.out_ids[:, s].copy_(nxt)
+        if self.hist is not None:
+            self.hist[:, self.T + s].copy_(nxt)
         self.tok.copy_(nxt[:, None])
         self.posid.add_(1)
 
-    def _ensure_graphs(self, gkey, steer, greedy, eos, pad):
+    def _ensure_graphs(self, gkey, steer, greedy, eos, pad, penalty=1.0):
         if gkey in self.graphs:
             return self.graphs[gkey]
         # warm-up on a side stream (lazy cuBLAS/SDPA init must not happen under capture)
@@ -758,7 +807,7 @@ class Session:
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(2):
-                self._step(1, steer, greedy, eos, pad)
+                self._step(1, steer, greedy, eos, pad, penalty)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         graphs = []
@@ -767,7 +816,7 @@ class Session:
                 g = torch.cuda.CUDAGraph()
                 before = dict(self.eng.counters)
                 with torch.cuda.graph(g, pool=self.pool):
-                    self._step(s, steer, greedy, eos, pad)
+                    self._step(s, steer, greedy, eos, pad, penalty)
                 # launches recorded into this graph (they did not run): credited on every replay instead
                 g.ia_launches = {k: self.eng.counters[k] - before[k] for k in before}
                 for k in before:
@@ -780,16 +829,32 @@ class Session:
 
     @torch.inference_mode()
     def generate(self, input_ids: torch.Tensor, attention_mask: torch.Tensor, steer: Optional[SteerSpec] = None,
-                 temperature: float = 0.0, top_k: Optional[int] = 50, eos_token_id: Optional[int] = None,
+                 temperature: float = 0.0, top_k: Optional[int] = 50, eos_token_id=None,
                  pad_token_id: int = 0, generator: Optional[torch.Generator] = None,
-                 keep_logits: bool = False) -> torch.Tensor:
+                 keep_logits: bool = False, top_p: Optional[float] = None, repetition_penalty: float = 1.0,
+                 do_sample: Optional[bool] = None) -> torch.Tensor:
         """Prefill + N-1 cached decode steps.  Returns new token ids [B, N] (device tensor owned by
-        the session; clone to keep).  With keep_logits, self.step_logits holds [N] x [B,V] float32."""
+        the session; clone to keep).  With keep_logits, self.step_logits holds [N] x [B,V] float32 (raw logits,
+        HF's `output_logits`).  eos_token_id: one id or a sequence of ids (HF stops a row on any of them).
+        do_sample None = sample iff temperature > 0; the warpers follow HF's order: repetition penalty,
+        temperature, top-k, top-p."""
         eng = self.eng
         ids = input_ids.to(eng.device, non_blocking=True)
         mask = attention_mask.to(eng.device, non_blocking=True)
         assert ids.shape == (self.B, self.T), (ids.shape, self.B, self.T)
-        greedy = temperature <= 0
+        greedy = (temperature <= 0) if do_sample is None else not do_sample
+        if not greedy and temperature <= 0:
+            raise ValueError("sampling needs a positive temperature")
+        eos_token_id = _eos_tuple(eos_token_id)
+        penalty = float(repetition_penalty or 1.0)
+        if penalty != 1.0:
+            if self._hist_buf is None:  # allocated once: decode graphs captured with a penalty point at it
+                self._hist_buf = torch.zeros(self.B, self.T + self.N, dtype=torch.long, device=eng.device)
+            self.hist = self._hist_buf
+            self.hist[:, : self.T].copy_(ids)
+            self.hist[:, self.T:] = ids[:, :1]
+        else:
+            self.hist = None
         self.step_logits = []
         st = None
         if steer is not None:
@@ -816,7 +881,8 @@ class Session:
         if keep_logits:
             self.step_logits.append(lg.float().clone())
         self.posid.copy_((mask.long().sum(-1, keepdim=True)) - 1)  # position of the last prompt token
-        nxt = lg.argmax(dim=-1) if greedy else self._sample(lg, temperature, top_k, generator)
+        lgp = self._penalise(lg, penalty)
+        nxt = lgp.argmax(dim=-1) if greedy else self._sample(lgp, temperature, top_k, generator, top_p)
         self._commit(nxt, 0, eos_token_id, pad_token_id)  # also advances posid to the new token's position
 
         # ---- decode ----
@@ -828,12 +894,13 @@ class Session:
             graphs = None
             if self.use_graphs:
                 gkey = (None if st is None else (st.layer_idx, st.row_t0 is None), greedy, eos_token_id, pad_token_id,
-                        self.logits_buf is not None)
+                        self.logits_buf is not None, penalty if greedy else 1.0)
                 if gkey not in self.graphs:
                     # capturing runs warm-up steps that scribble on the state: save and restore it
-                    keep = (self.tok.clone(), self.posid.clone(), self.out_ids.clone(), self.unfinished.clone())
-                    graphs = self._ensure_graphs(gkey, st, greedy, eos_token_id, pad_token_id)
-                    for dst, src in zip((self.tok, self.posid, self.out_ids, self.unfinished), keep):
+                    state = [self.tok, self.posid, self.out_ids, self.unfinished] + ([self.hist] if self.hist is not None else [])
+                    keep = [t.clone() for t in state]
+                    graphs = self._ensure_graphs(gkey, st, greedy, eos_token_id, pad_token_id, penalty)
+                    for dst, src in zip(state, keep):
                         dst.copy_(src)
                 graphs = self.graphs[gkey]
             for s in range(1, self.N):
@@ -842,11 +909,11 @@ class Session:
                     for k, v in graphs[s - 1].ia_launches.items():
                         eng.counters[k] += v
                 else:
-                    self._step(s, st, greedy, eos_token_id, pad_token_id)
+                    self._step(s, st, greedy, eos_token_id, pad_token_id, penalty)
                 if keep_logits:
                     self.step_logits.append(self.logits_buf.float().clone())
                 if not greedy:
-                    nxt = self._sample(self.logits_buf, temperature, top_k, generator)
+                    nxt = self._sample(self._penalise(self.logits_buf, penalty), temperature, top_k, generator, top_p)
                     self._commit(nxt, s, eos_token_id, pad_token_id)
                 if eos_token_id is not None and s % 16 == 0 and not bool(self.unfinished.any()):
                     self.out_ids[:, s + 1:].fill_(pad_token_id)
@@ -854,17 +921,39 @@ class Session:
         return self.out_ids
 
     @staticmethod
-    def sampling_probs(logits: torch.Tensor, temperature: float, top_k: Optional[int]) -> torch.Tensor:
-        """The distribution HF `generate(do_sample=True, temperature=...)` samples from with its default
-        generation config: temperature scaling, then top-k 50 (TemperatureLogitsWarper,
-        TopKLogitsWarper), then softmax.  reference model_utils.py:833-837 passes only temperature."""
+    def sampling_probs(logits: torch.Tensor, temperature: float, top_k: Optional[int], top_p: Optional[float] = None
+                       ) -> torch.Tensor:
+        """The distribution HF `generate(do_sample=True, temperature=...)` samples from: temperature scaling, then
+        top-k, then top-p (TemperatureLogitsWarper, TopKLogitsWarper, TopPLogitsWarper in that order), then softmax.
+        reference model_utils.py:833-837 passes only the temperature; top_k / top_p come from the checkpoint's
+        generation_config (top_k 50 by default; Llama-3.1 ships top_p 0.9, Qwen2.5 top_k 20 / top_p 0.8)."""
         lg = logits.float() / temperature
         if top_k is not None and 0 < top_k < lg.shape[-1]:
             kth = lg.topk(top_k, dim=-1).values[..., -1:]
             lg = lg.masked_fill(lg < kth, float("-inf"))
+        if top_p is not None and 0.0 < top_p < 1.0:
+            # drop the low-probability tail whose cumulative mass stays within 1 - top_p; the most likely token
+            # always survives
+            asc, order = torch.sort(lg, dim=-1, descending=False)
+            tail = asc.softmax(dim=-1).cumsum(dim=-1) <= (1.0 - top_p)
+            tail[..., -1] = False
+            lg = lg.masked_fill(tail.scatter(-1, order, tail), float("-inf"))
         return torch.softmax(lg, dim=-1)
 
     @staticmethod
-    def _sample(logits: torch.Tensor, temperature: float, top_k: Optional[int], generator) -> torch.Tensor:
-        probs = Session.sampling_probs(logits, temperature, top_k)
+    def _sample(logits: torch.Tensor, temperature: float, top_k: Optional[int], generator,
+                top_p: Optional[float] = None) -> torch.Tensor:
+        probs = Session.sampling_probs(logits, temperature, top_k, top_p)
         return torch.multinomial(probs, 1, generator=generator).squeeze(-1)
+
+
+def _eos_tuple(eos) -> Optional[tuple]:
+    """None, one id or any sequence of ids -> a sorted tuple (hashable: part of the decode-graph key) or None."""
+    if eos is None:
+        return None
+    if isinstance(eos, int):
+        return (int(eos),)
+    if isinstance(eos, torch.Tensor):
+        eos = eos.flatten().tolist()
+    ids = tuple(sorted({int(e) for e in eos}))
+    return ids or None

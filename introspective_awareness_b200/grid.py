@@ -21,26 +21,71 @@ from . import steering_utils as su
 @dataclass(frozen=True)
 class Trial:
     concept: str
-    strength: float      # 0.0 for control rows
-    trial: int
-    kind: str            # "injection" | "control" | "forced"
+    strength: float      # the configuration's strength (control rows carry it too, they are not steered)
+    trial: int           # the number in the "Trial N" prompt and in the result's "trial" field
+    kind: str            # "injection" | "control" | "forced_injection"
 
 
 def layer_trials(concepts: Sequence[str], strengths: Sequence[float], n_injection: int, n_control: int = 0,
                  n_forced: int = 0, dedupe_control: bool = True) -> List[Trial]:
     """Rows of one layer's batch, concept-major like the reference's task lists
-    (detect_injected_thoughts.py:1797-1799).  Control trials depend on neither layer nor strength;
-    the reference regenerates them for every (layer, strength) (:1908 sits inside both loops) —
-    with dedupe_control they appear once per layer batch instead of once per strength."""
+    (detect_injected_thoughts.py:1797-1799), numbered as the driver numbers them: injection trials
+    1..n_injection, control trials n_injection + t (:1917), forced trials n_injection + n_control + t (:1984).
+    Control trials depend on neither layer nor strength; the reference regenerates them for every
+    (layer, strength) (:1908 sits inside both loops) — with dedupe_control they appear once per layer
+    batch (strength 0.0) instead of once per strength."""
     rows: List[Trial] = []
     for a in strengths:
         rows += [Trial(c, float(a), t, "injection") for c in concepts for t in range(1, n_injection + 1)]
-        rows += [Trial(c, float(a), t, "forced") for c in concepts for t in range(1, n_forced + 1)]
         if not dedupe_control:
-            rows += [Trial(c, 0.0, t, "control") for c in concepts for t in range(1, n_control + 1)]
+            rows += [Trial(c, float(a), n_injection + t, "control") for c in concepts for t in range(1, n_control + 1)]
+        rows += [Trial(c, float(a), n_injection + n_control + t, "forced_injection")
+                 for c in concepts for t in range(1, n_forced + 1)]
     if dedupe_control:
-        rows += [Trial(c, 0.0, t, "control") for c in concepts for t in range(1, n_control + 1)]
+        rows += [Trial(c, 0.0, n_injection + t, "control") for c in concepts for t in range(1, n_control + 1)]
     return rows
+
+
+# The sweep driver's forced-identification trial is NOT steering_utils' forced-noticing prompt: its own
+# explanation, its own question, no generation prompt, and an assistant prefill appended to the templated text
+# (detect_injected_thoughts.py:1984-2010).
+DRIVER_FORCED_EXPLANATION = (
+    "I am an interpretability researcher studying transformer-based language models like you. "
+    "I have access to the internals of your neural network. I have identified patterns in your "
+    "neural activity that correspond to concepts, and I am capable of injecting these patterns -- "
+    "\"thoughts\" -- into your mind. I want to assess how well you can detect when I inject thoughts. "
+    "I will inject a thought about a specific word on each trial."
+)
+DRIVER_FORCED_PREFILL = "I notice an injected thought about"
+
+
+def driver_messages(trial_number: int, forced: bool) -> List[dict]:
+    """The four-message conversation the driver builds for a trial (:1812-1828 / :1918-1932 detection and control,
+    :1985-1998 forced)."""
+    if not forced:
+        return su.trial_messages(trial_number, forced=False)
+    return [
+        {"role": "system", "content": ""},
+        {"role": "user", "content": DRIVER_FORCED_EXPLANATION},
+        {"role": "assistant", "content": "Ok."},
+        {"role": "user", "content": f"Trial {trial_number}: What injected thought do you notice?"},
+    ]
+
+
+def driver_prompt(model, trial_number: int, forced: bool) -> str:
+    """Templated prompt text exactly as the driver produces it: system turn filtered for models without a system
+    role, chat template with a generation prompt for detection / control trials (:1833-1840), chat template
+    WITHOUT one plus the prefill for forced trials (:2004-2017); plain-text fallback when the tokenizer has no
+    chat template."""
+    msgs = driver_messages(trial_number, forced)
+    tok = model.tokenizer
+    if hasattr(tok, "apply_chat_template"):
+        filtered = filter_messages_for_model(msgs, getattr(model, "model_name", ""))
+        if forced:
+            return tok.apply_chat_template(filtered, tokenize=False, add_generation_prompt=False) + DRIVER_FORCED_PREFILL
+        return tok.apply_chat_template(filtered, tokenize=False, add_generation_prompt=True)
+    tail = f" {DRIVER_FORCED_PREFILL}" if forced else ""
+    return f"{msgs[1]['content']}\n\nAssistant: {msgs[2]['content']}\n\nUser: {msgs[3]['content']}\n\nAssistant:{tail}"
 
 
 # Chat templates of these registry names reject a system turn (reference detect_injected_thoughts.py:80-81).
@@ -72,17 +117,16 @@ def run_layer(model, layer_idx: int, vectors: Dict[str, torch.Tensor], rows: Seq
     for part in chunk(rows, batch_size):
         prompts, starts = [], []
         for r in part:
-            key = (r.trial, r.kind == "forced")
+            key = (r.trial, r.kind == "forced_injection")
             if key not in prompt_cache:
-                msgs = filter_messages_for_model(su.trial_messages(r.trial, key[1]), getattr(model, "model_name", ""))
-                p = su.format_trial_prompt(model, r.trial, forced=key[1], messages=msgs)
+                p = driver_prompt(model, r.trial, forced=key[1])
                 prompt_cache[key] = (p, su.steering_start_position(model, p, r.trial, missing=0))
             p, t0 = prompt_cache[key]
             prompts.append(p)
             starts.append(t0)
         ids, mask = model._encode(prompts)
         row_vec = [cidx[r.concept] if r.kind != "control" else -1 for r in part]
-        alphas = [r.strength for r in part]
+        alphas = [r.strength if r.kind != "control" else 0.0 for r in part]
         new_ids = model.steered_generate_ids(ids, mask, layer_idx, table, row_vec, alphas, starts, max_new_tokens,
                                              temperature)
         texts = model._decode_rows(new_ids, ids, mask)

@@ -10,8 +10,10 @@ from typing import Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import (IA_BF16, IA_F16, IA_F32, IA_IMPL_ADD_STAGED, IA_IMPL_REGS, IA_IMPL_TMA, IA_MODE_BASELINE, IA_MODE_POSNEG, IA_MODE_RAW,
-                   IA_MODE_SIMPLE, IA_NORM_GEMMA, IA_NORM_LLAMA, IA_RSQRT_IEEE, IA_STEER_ALL, check)
+from ._lib import (IA_BF16, IA_F16, IA_F32, IA_IMPL_ADD_STAGED, IA_IMPL_REGS, IA_IMPL_STREAM, IA_IMPL_TMA, IA_MODE_BASELINE,
+                   IA_MODE_POSNEG, IA_MODE_RAW, IA_MODE_SIMPLE, IA_NORM_GEMMA, IA_NORM_LLAMA, IA_RSQRT_IEEE, IA_STEER_ALL, check)
+
+_IMPL = {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS, "add_staged": IA_IMPL_ADD_STAGED, "stream": IA_IMPL_STREAM}
 
 _DTYPES = {torch.bfloat16: IA_BF16, torch.float16: IA_F16, torch.float32: IA_F32}
 MODES = {"baseline": IA_MODE_BASELINE, "simple": IA_MODE_SIMPLE, "no_baseline": IA_MODE_RAW, "raw": IA_MODE_RAW,
@@ -42,37 +44,49 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+def _tap(cap_out: Optional[torch.Tensor], cap_tok: Optional[torch.Tensor], cap_t: int, rows: int, hid: int, dtype):
+    if cap_out is None:
+        return 0, 0, 0
+    if tuple(cap_out.shape) != (rows, hid):
+        raise ValueError("cap_out must be [rows, H]")
+    return _cuda(cap_out, "cap_out", dtype), _cuda(cap_tok, "cap_tok", torch.int32), int(cap_t)
+
+
 def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: str,
                    vtable: Optional[torch.Tensor] = None, row_vec: Optional[torch.Tensor] = None,
                    row_alpha: Optional[torch.Tensor] = None, row_t0: Optional[torch.Tensor] = None,
                    pos0: int = 0, steer_all: bool = False, out: Optional[torch.Tensor] = None,
-                   ieee_rsqrt: bool = False, impl: str = "auto", add: Optional[torch.Tensor] = None) -> torch.Tensor:
+                   ieee_rsqrt: bool = False, impl: str = "auto", add: Optional[torch.Tensor] = None,
+                   cap_out: Optional[torch.Tensor] = None, cap_tok: Optional[torch.Tensor] = None, cap_t: int = -1
+                   ) -> torch.Tensor:
     """K2.  `h` [rows, T, H] is updated in place with the per-row injection; returns y = RMSNorm(h').
-    With row_vec None this is a plain RMSNorm of `variant`.  impl: "auto" | "regs" | "tma".
+    With row_vec None this is a plain RMSNorm of `variant`.  impl: "auto" | "regs" | "tma" | "stream".
     add: a branch output [rows, T, H] that is added to h first (h <- h + add, rounded), the decoder
-    layer's residual add folded into the same pass; h is then rewritten for every vector."""
+    layer's residual add folded into the same pass; h is then rewritten for every vector.
+    cap_out [rows, H]: capture tap — also receives the UPDATED row of position cap_tok[b] (int32 [rows]) or,
+    without cap_tok, position cap_t (-1 = last) of every row."""
     if h.dim() != 3:
         raise ValueError("h must be [rows, T, H]")
     rows, t_len, hid = h.shape
     y = torch.empty_like(h) if out is None else out
-    flags = ((IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
-             | {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS, "add_staged": IA_IMPL_ADD_STAGED}[impl])
+    flags = (IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0) | _IMPL[impl]
+    tap = _tap(cap_out, cap_tok, cap_t, rows, hid, h.dtype)
     lib = _lib.load()
     if add is not None:
         if add.shape != h.shape:
             raise ValueError("add must have the shape of h")
-        rc = lib.ia_add_inject_rmsnorm(
+        rc = lib.ia_add_inject_rmsnorm_tap(
             _cuda(h, "h"), _cuda(add, "add", h.dtype), _cuda(y, "out", h.dtype), _cuda(vtable, "vtable"),
             _cuda(row_vec, "row_vec", torch.int32), _cuda(row_alpha, "row_alpha", torch.float32),
             _cuda(row_t0, "row_t0", torch.int32), _cuda(weight, "weight", h.dtype), float(eps), rows, t_len, hid, int(pos0),
-            _dt(h), _dt(vtable) if vtable is not None else _dt(h), VARIANTS[variant], flags, _stream())
+            _dt(h), _dt(vtable) if vtable is not None else _dt(h), VARIANTS[variant], flags, *tap, _stream())
         check(rc, "ia_add_inject_rmsnorm")
         return y
-    rc = lib.ia_inject_rmsnorm(
+    rc = lib.ia_inject_rmsnorm_tap(
         _cuda(h, "h"), _cuda(y, "out", h.dtype), _cuda(vtable, "vtable"), _cuda(row_vec, "row_vec", torch.int32),
         _cuda(row_alpha, "row_alpha", torch.float32), _cuda(row_t0, "row_t0", torch.int32),
         _cuda(weight, "weight", h.dtype), float(eps), rows, t_len, hid, int(pos0), _dt(h),
-        _dt(vtable) if vtable is not None else _dt(h), VARIANTS[variant], flags, _stream())
+        _dt(vtable) if vtable is not None else _dt(h), VARIANTS[variant], flags, *tap, _stream())
     check(rc, "ia_inject_rmsnorm")
     return y
 
@@ -80,20 +94,22 @@ def inject_rmsnorm(h: torch.Tensor, weight: torch.Tensor, eps: float, variant: s
 def gemma2_tail_inject_rmsnorm(mlp_out: torch.Tensor, residual: torch.Tensor, w_post: torch.Tensor,
                                w_next: torch.Tensor, eps: float, vtable=None, row_vec=None, row_alpha=None,
                                row_t0=None, pos0: int = 0, steer_all: bool = False,
-                               out: Optional[torch.Tensor] = None, ieee_rsqrt: bool = False, impl: str = "auto") -> torch.Tensor:
+                               out: Optional[torch.Tensor] = None, ieee_rsqrt: bool = False, impl: str = "auto",
+                               cap_out: Optional[torch.Tensor] = None, cap_tok: Optional[torch.Tensor] = None,
+                               cap_t: int = -1) -> torch.Tensor:
     """K2 Gemma-2 block tail: residual <- inject(residual + gemma_norm(mlp_out; w_post)), returns
-    gemma_norm(residual; w_next)."""
+    gemma_norm(residual; w_next).  cap_out / cap_tok / cap_t: capture tap as in `inject_rmsnorm`."""
     rows, t_len, hid = residual.shape
     y = torch.empty_like(residual) if out is None else out
-    flags = ((IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0)
-             | {"auto": 0, "tma": IA_IMPL_TMA, "regs": IA_IMPL_REGS}[impl])
+    flags = (IA_STEER_ALL if steer_all else 0) | (IA_RSQRT_IEEE if ieee_rsqrt else 0) | _IMPL[impl]
+    tap = _tap(cap_out, cap_tok, cap_t, rows, hid, residual.dtype)
     lib = _lib.load()
-    rc = lib.ia_gemma2_tail_inject_rmsnorm(
+    rc = lib.ia_gemma2_tail_inject_rmsnorm_tap(
         _cuda(mlp_out, "mlp_out", residual.dtype), _cuda(residual, "residual"), _cuda(y, "out", residual.dtype),
         _cuda(vtable, "vtable"), _cuda(row_vec, "row_vec", torch.int32), _cuda(row_alpha, "row_alpha", torch.float32),
         _cuda(row_t0, "row_t0", torch.int32), _cuda(w_post, "w_post", residual.dtype),
         _cuda(w_next, "w_next", residual.dtype), float(eps), rows, t_len, hid, int(pos0), _dt(residual),
-        _dt(vtable) if vtable is not None else _dt(residual), flags, _stream())
+        _dt(vtable) if vtable is not None else _dt(residual), flags, *tap, _stream())
     check(rc, "ia_gemma2_tail_inject_rmsnorm")
     return y
 
@@ -175,6 +191,51 @@ def gather_meandiff(concept_layers: Sequence[torch.Tensor], base_layers: Optiona
     check(rc, "ia_gather_meandiff")
     # keep index/pointer tensors alive until the launch is enqueued (it is, the call is synchronous on the host)
     return out_f32, out_r, out_n
+
+
+def meandiff_compact(concept_acts: torch.Tensor, base_acts: Optional[torch.Tensor], mode: str = "baseline",
+                     normalize: bool = False, want_f32: bool = True, want_norm: bool = True,
+                     workspace: Optional[torch.Tensor] = None
+                     ) -> Tuple[Optional[torch.Tensor], torch.Tensor, Optional[torch.Tensor]]:
+    """K1 over compact rows (what K2's tap leaves behind): concept_acts [L, C, H], base_acts [L, Nb, H] or None.
+    Returns (v_f32 [L, n_out, H] or None, v_rounded [L, n_out, H] model dtype, norm [L, n_out] or None)."""
+    if concept_acts.dim() != 3:
+        raise ValueError("concept_acts must be [n_layers, n_concept, H]")
+    n_layers, n_concept, hid = concept_acts.shape
+    dev, dtype = concept_acts.device, concept_acts.dtype
+    imode = MODES[mode]
+    n_base = 0
+    if imode != IA_MODE_RAW:
+        if base_acts is None or base_acts.dim() != 3 or base_acts.shape[0] != n_layers or base_acts.shape[2] != hid:
+            raise ValueError("base_acts must be [n_layers, n_base, H]")
+        n_base = base_acts.shape[1]
+    n_out = 1 if imode == IA_MODE_POSNEG else n_concept
+    out_f32 = torch.empty((n_layers, n_out, hid), dtype=torch.float32, device=dev) if want_f32 else None
+    out_r = torch.empty((n_layers, n_out, hid), dtype=dtype, device=dev)
+    out_n = torch.empty((n_layers, n_out), dtype=torch.float32, device=dev) if want_norm else None
+    need = workspace_bytes(n_layers, n_concept, n_base, hid, mode)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+    rc = _lib.load().ia_meandiff_compact(
+        _cuda(concept_acts, "concept_acts"), n_concept, _cuda(base_acts if imode != IA_MODE_RAW else None, "base_acts", dtype),
+        n_base, n_layers, hid, imode, int(bool(normalize)), _cuda(out_f32, "out_f32"), out_r.data_ptr(), _cuda(out_n, "out_norm"),
+        workspace.data_ptr(), workspace.numel() * workspace.element_size(), _dt(concept_acts), _stream())
+    check(rc, "ia_meandiff_compact")
+    return out_f32, out_r, out_n
+
+
+def segsum_compact(rows: torch.Tensor) -> torch.Tensor:
+    """K1a over compact rows [L, n, H]: fp32 column sums [L, H] (the rank-local half of sharded extraction)."""
+    n_layers, n_rows, hid = rows.shape
+    if n_rows == 0:  # a rank that holds none of the rows contributes an exact zero
+        return torch.zeros((n_layers, hid), dtype=torch.float32, device=rows.device)
+    out_sum = torch.empty((n_layers, hid), dtype=torch.float32, device=rows.device)
+    need = workspace_bytes(n_layers, 0, n_rows, hid, "baseline")
+    ws = torch.empty(max(need, 256), dtype=torch.uint8, device=rows.device)
+    rc = _lib.load().ia_segsum_compact(_cuda(rows, "rows"), n_rows, n_layers, hid, out_sum.data_ptr(), ws.data_ptr(), ws.numel(),
+                                       _dt(rows), _stream())
+    check(rc, "ia_segsum_compact")
+    return out_sum
 
 
 def gather_segsum(layers: Sequence[torch.Tensor], rows=None, tok=None, n_rows: Optional[int] = None,

@@ -54,7 +54,7 @@ MODEL_NAME_MAP = {
 class ModelWrapper:
     def __init__(self, model_name: str, device: str = "cuda", dtype: torch.dtype = torch.bfloat16,
                  quantization_config=None, *, model=None, tokenizer=None, compat_slice: bool = False,
-                 attention: str = "hf"):
+                 attention: str = "auto"):
         self.model_name = model_name
         self.device = device
         self.dtype = dtype
@@ -81,7 +81,7 @@ class ModelWrapper:
     # -- construction helpers -----------------------------------------------------------------
     @classmethod
     def from_arch(cls, arch: str, device: str = "cuda", dtype: torch.dtype = torch.bfloat16, seed: Optional[int] = 0,
-                  tokenizer=None, attention: str = "hf", **overrides) -> "ModelWrapper":
+                  tokenizer=None, attention: str = "auto", **overrides) -> "ModelWrapper":
         """Random-init model of a named architecture + stub tokenizer (offline)."""
         from .stub_tokenizer import StubTokenizer
         from .synthetic import build_model
@@ -104,12 +104,32 @@ class ModelWrapper:
         enc = self.tokenizer(list(prompts), return_tensors="pt", padding=True, truncation=True)
         return enc["input_ids"], enc["attention_mask"]
 
-    def _eos(self) -> Optional[int]:
+    def _eos(self):
+        """Every id of the checkpoint's EOS set (generation_config.eos_token_id may be a list: Llama-3.x-Instruct
+        [128001, 128008, 128009], Gemma-2-it [1, 107]); HF `generate` ends a row on any of them."""
         gc_ = getattr(self.model, "generation_config", None)
         eos = getattr(gc_, "eos_token_id", None) if gc_ is not None else None
         if isinstance(eos, (list, tuple)):
-            eos = eos[0] if eos else None
+            eos = tuple(int(e) for e in eos) or None
         return eos
+
+    def _generation_settings(self, temperature: float, generation_kwargs: dict) -> dict:
+        """What reference model_utils.py:828-847 hands to HF `generate`, resolved the way `generate` resolves it:
+        the caller's temperature switches sampling on and carries **generation_kwargs (:833-837); everything it does
+        not set comes from the checkpoint's generation_config — top_k / top_p / repetition_penalty, and with
+        temperature == 0 also do_sample and the temperature themselves (the reference passes neither then, so a
+        checkpoint that ships do_sample=True still samples)."""
+        gc_ = getattr(self.model, "generation_config", None)
+        cfg = lambda k, d: d if gc_ is None or getattr(gc_, k, None) is None else getattr(gc_, k)
+        if temperature > 0:
+            over = dict(generation_kwargs)
+            do_sample, temp = bool(over.get("do_sample", True)), float(over.get("temperature", temperature))
+        else:
+            over = {}
+            do_sample, temp = bool(cfg("do_sample", False)), float(cfg("temperature", 1.0))
+        pick = lambda k, d: over[k] if k in over else cfg(k, d)
+        return dict(do_sample=do_sample, temperature=temp if do_sample else 0.0, top_k=pick("top_k", 50),
+                    top_p=pick("top_p", 1.0), repetition_penalty=float(pick("repetition_penalty", 1.0)))
 
     def _decode_rows(self, new_ids: torch.Tensor, input_ids: torch.Tensor, attention_mask: torch.Tensor) -> List[str]:
         new_ids = new_ids.cpu()
@@ -132,22 +152,61 @@ class ModelWrapper:
                                   ) -> torch.Tensor:
         """[n_layers, B, H] CPU tensor in the model dtype: one forward for all layers."""
         ids, mask = self._encode(prompts)
-        _, rows, _ = self.engine.extract_vectors(ids, mask, None, None, layer_indices, mode="no_baseline",
-                                                 token_idx=token_idx, want_f32=False, want_norm=False)
-        return rows.cpu()
+        return self.engine.capture_rows(ids, mask, layer_indices, token_idx).cpu()
 
     def extract_concept_vectors(self, concept_prompts: List[str], baseline_prompts: Optional[List[str]],
                                 layer_indices: Sequence[int], method: str = "baseline", normalize: bool = False,
-                                token_idx: int = -1, fp32: bool = False) -> torch.Tensor:
+                                token_idx: int = -1, fp32: bool = False, sharded: bool = False) -> torch.Tensor:
         """Fused K1 path: [n_layers, n_out, H] CPU tensor — the reference-rounded vectors in the model
-        dtype, or with fp32=True the un-rounded fp32-accumulate vectors."""
+        dtype, or with fp32=True the un-rounded fp32-accumulate vectors.
+        sharded=True (a collective call: every rank of the `torch.distributed` job must make it with the same
+        arguments) splits the prompts over the ranks, see `extract_concept_vectors_sharded`."""
         cids, cmask = self._encode(concept_prompts)
         bids = bmask = None
         if method not in ("no_baseline", "raw"):
             bids, bmask = self._encode(baseline_prompts)
-        v32, vr, _ = self.engine.extract_vectors(cids, cmask, bids, bmask, layer_indices, mode=method,
-                                                 normalize=normalize, token_idx=token_idx, want_f32=fp32, want_norm=False)
+        if sharded:
+            v32, vr, _ = self.extract_vectors_sharded_ids(cids, cmask, bids, bmask, layer_indices, method, normalize,
+                                                          token_idx, want_f32=fp32)
+        else:
+            v32, vr, _ = self.engine.extract_vectors(cids, cmask, bids, bmask, layer_indices, mode=method,
+                                                     normalize=normalize, token_idx=token_idx, want_f32=fp32, want_norm=False)
         return (v32 if fp32 else vr).cpu()
+
+    def extract_vectors_sharded_ids(self, concept_ids, concept_mask, base_ids, base_mask, layer_indices: Sequence[int],
+                                    method: str = "baseline", normalize: bool = False, token_idx: int = -1,
+                                    want_f32: bool = False):
+        """Prompt-sharded K1: every rank forwards its contiguous slice of the concept prompts and of
+        the baseline prompts (captured rows land compactly through K2's tap), K1a sums its baseline rows in fp32,
+        the [L, H] sums are all-reduced and the concept rows all-gathered (NCCL; gloo on CPU test rigs), and K1b
+        finishes on every rank — rounding to the model dtype happens after the reduce.  Token-level entry point;
+        returns (v_f32 | None, v_rounded, norm) on the device, identical on every rank.  The slices keep the padded
+        width of the whole batch, so every row sees the positions it would see un-sharded."""
+        from . import kernels, parallel
+
+        if method == "posneg":
+            raise ValueError("pos/neg mean difference is not sharded: call the un-sharded path")
+        layer_indices = [int(i) for i in layer_indices]
+        eng = self.engine
+        n_concept = concept_ids.shape[0]
+        n_base = 0 if base_ids is None else base_ids.shape[0]
+
+        def capture_rows_and_sum(segment, lo, hi):
+            ids, mask = (concept_ids, concept_mask) if segment == "concept" else (base_ids, base_mask)
+            if hi > lo:
+                rows = eng.capture_rows(ids[lo:hi], mask[lo:hi], layer_indices, token_idx, slot=0 if segment == "concept" else 1)
+            else:  # more ranks than prompts: this rank contributes nothing to this segment
+                rows = torch.empty((len(layer_indices), 0, eng.hidden), dtype=eng.dtype, device=eng.device)
+            if segment == "concept":
+                return rows, None
+            eng.counters["k1_launches"] += 1
+            return None, kernels.segsum_compact(rows)
+
+        def finalize(rows, base_sum, n_base_total, mode, norm):
+            eng.counters["k1_launches"] += 2 if norm else 1
+            return kernels.meandiff_finalize(rows.contiguous(), base_sum, n_base_total, mode, norm, want_f32=want_f32)
+
+        return parallel.extract_vectors_sharded(capture_rows_and_sum, finalize, n_concept, n_base, method, normalize)
 
     # -- generation ---------------------------------------------------------------------------
     def steered_generate_ids(self, input_ids: torch.Tensor, attention_mask: torch.Tensor, layer_idx: Optional[int],
@@ -163,6 +222,10 @@ class ModelWrapper:
         if layer_idx is not None and vtable is not None:
             if dev.type != "cuda":
                 raise RuntimeError("steered generation needs the CUDA kernels; there is no CPU path")
+            rv = torch.as_tensor(row_vec, dtype=torch.int64)
+            if rv.numel() != b or (rv.numel() and int(rv.max()) >= int(vtable.shape[0])):
+                raise IndexError(f"row_vec must hold {b} indices below the table's {int(vtable.shape[0])} rows "
+                                 "(negative = control row)")
             t0 = None
             if start_positions is not None:
                 pads = t - attention_mask.sum(dim=1)
@@ -176,8 +239,10 @@ class ModelWrapper:
         sess = self.engine.session(b, t, max_new_tokens, padded, n_vec_cap=n_vec_cap,
                                    vec_dtype=None if vtable is None else vtable.dtype)
         self.last_session = sess
-        return sess.generate(input_ids, attention_mask, steer, temperature=temperature,
-                             top_k=generation_kwargs.get("top_k", 50), eos_token_id=self._eos(),
+        gs = self._generation_settings(temperature, generation_kwargs)
+        return sess.generate(input_ids, attention_mask, steer, temperature=gs["temperature"], top_k=gs["top_k"],
+                             top_p=gs["top_p"], repetition_penalty=gs["repetition_penalty"], do_sample=gs["do_sample"],
+                             eos_token_id=self._eos(),
                              pad_token_id=self.tokenizer.pad_token_id if self.tokenizer is not None else 0,
                              generator=generator, keep_logits=keep_logits)
 

@@ -87,6 +87,16 @@ def gather_to_rank0(t: torch.Tensor) -> Optional[List[torch.Tensor]]:
     return parts if r == 0 else None
 
 
+def gather_objects_to_rank0(obj) -> Optional[list]:
+    """One picklable object from every rank, in rank order, on rank 0 (None elsewhere): the sweep's result rows."""
+    r, w = world()
+    if w == 1:
+        return [obj]
+    parts = [None] * w if r == 0 else None
+    dist.gather_object(obj, parts, dst=0)
+    return parts
+
+
 def extract_vectors_sharded(capture_rows_and_sum: Callable, finalize: Callable, n_concept: int, n_base: int,
                             mode: str = "baseline", normalize: bool = False):
     """Prompt-sharded K1.

@@ -37,19 +37,18 @@ def config_dir(base: Path, layer_fraction: float, strength: float) -> Path:
 
 
 def keyword_metrics(results: Sequence[dict]) -> Dict[str, float]:
-    """Detection / identification rates from the `detected` keyword flag, named as the reference
-    names its per-config metrics (detect_injected_thoughts.py:2139-2150)."""
+    """What the reference driver writes as a configuration's metrics when its LLM judge is off (the judge stays
+    outside this package): keyword rates from the `detected` flag, and zeros for the three figures only the judge
+    can produce (detect_injected_thoughts.py:2108-2120, names and order as in :2139-2150)."""
     def rate(rows):
         rows = list(rows)
-        return sum(bool(r["detected"]) for r in rows) / len(rows) if rows else 0.0
+        return sum(1 for r in rows if r["detected"]) / len(rows) if rows else 0
 
-    inj = [r for r in results if r["trial_type"] == "injection"]
-    ctl = [r for r in results if r["trial_type"] == "control"]
-    frc = [r for r in results if r["trial_type"] == "forced"]
-    hit, fa = rate(inj), rate(ctl)
-    n = len(inj) + len(ctl)
-    acc = (sum(bool(r["detected"]) for r in inj) + sum(not r["detected"] for r in ctl)) / n if n else 0.0
-    return {"detection_hit_rate": hit, "detection_false_alarm_rate": fa, "detection_accuracy": acc,
+    inj = [r for r in results if r["injected"] and r["trial_type"] == "injection"]
+    ctl = [r for r in results if not r["injected"] and r["trial_type"] == "control"]
+    frc = [r for r in results if r["trial_type"] == "forced_injection"]
+    return {"detection_hit_rate": rate(inj), "detection_false_alarm_rate": rate(ctl), "detection_accuracy": 0,
+            "identification_accuracy_given_claim": 0, "combined_detection_and_identification_rate": 0,
             "forced_identification_accuracy": rate(frc)}
 
 
@@ -81,17 +80,22 @@ def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], lay
               strengths: Sequence[float], n_trials: int = 30, max_new_tokens: int = 100, temperature: float = 1.0,
               batch_size: int = 256, output_dir: Optional[str] = None, extraction_method: str = "baseline",
               with_forced: bool = True, save_vector_files: bool = True) -> Dict[tuple, List[dict]]:
-    """Runs the whole grid; returns {(layer_fraction, strength): results} for the layers this rank owns
-    and (if output_dir) writes the reference's files for them.  Trial split as the reference:
-    n_injection = n_trials // 2, n_control = n_trials - n_injection, forced = n_injection
-    (detect_injected_thoughts.py:1792-1799)."""
+    """Runs the whole grid and (if output_dir) writes the reference's files.  Trial split as the reference:
+    n_injection = n_trials // 2, n_control = n_trials - n_injection, forced = n_injection, numbered 1..n_injection,
+    then n_injection + t, then n_injection + n_control + t (detect_injected_thoughts.py:1792-1799, :1917, :1984).
+
+    In a `torch.distributed` job (one process per GPU, `parallel.init_from_env`) this is a collective call:
+    extraction is prompt-sharded (every rank forwards its slice of the concept and baseline prompts, fp32 sums
+    all-reduced, concept rows all-gathered), each rank steers the layer fractions dealt to it round-robin and
+    writes their files, and the result rows are gathered: rank 0 returns every configuration, the other ranks
+    their own."""
     rank, world = parallel.world()
     concepts = list(concepts)
     fractions = list(layer_fractions)
     layer_of = {f: get_layer_at_fraction(model, f) for f in fractions}
     uniq_layers = sorted(set(layer_of.values()))
     by_layer = vu.extract_concept_vectors_multi_layer(model, concepts, list(baseline_words), uniq_layers,
-                                                      extraction_method=extraction_method)
+                                                      extraction_method=extraction_method, sharded=world > 1)
     base = None
     if output_dir is not None:
         base = Path(output_dir) / str(model.model_name).replace("/", "_")
@@ -108,10 +112,17 @@ def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], lay
                                  layer_fraction=f)
         control = [r for r in results if r["trial_type"] == "control"]
         for a in strengths:
-            # the reference stores the (strength-independent) control trials in every strength's file
-            cfg = [r for r in results if r["trial_type"] != "control" and r["strength"] == float(a)]
+            # one file per (layer fraction, strength), rows in the driver's order: injection, control, forced
+            # (:1797-1799); the strength-independent control trials are stored in every strength's file
+            mine = [r for r in results if r["trial_type"] != "control" and r["strength"] == float(a)]
+            cfg = [r for r in mine if r["trial_type"] == "injection"]
             cfg += [dict(r, strength=float(a)) for r in control]
+            cfg += [r for r in mine if r["trial_type"] == "forced_injection"]
             out[(f, float(a))] = cfg
             if base is not None:
                 write_config(base, f, layer, float(a), cfg, temperature, max_new_tokens)
+    if world > 1:
+        parts = parallel.gather_objects_to_rank0(out)
+        if rank == 0:
+            out = {k: v for part in parts for k, v in part.items()}
     return out

@@ -90,11 +90,14 @@ _METHODS = ("baseline", "simple", "no_baseline", "posneg")
 
 
 def _vectors(model, concept_prompts: List[str], base_prompts: Optional[List[str]], layer_indices: Sequence[int],
-             method: str, normalize: bool, token_idx: int) -> torch.Tensor:
+             method: str, normalize: bool, token_idx: int, sharded: bool = False) -> torch.Tensor:
     """[n_layers, n_out, H] CPU tensor in the model dtype."""
     if method not in _METHODS:
         raise ValueError(f"Unknown extraction method: {method}")
     if hasattr(model, "extract_concept_vectors"):
+        if sharded:
+            return model.extract_concept_vectors(concept_prompts, base_prompts, layer_indices, method, normalize, token_idx,
+                                                 sharded=True)
         return model.extract_concept_vectors(concept_prompts, base_prompts, layer_indices, method, normalize, token_idx)
     # Foreign model object: take its activations, finish on the GPU with K1b.
     from . import kernels
@@ -154,9 +157,10 @@ def extract_concept_vector_no_baseline(model, concept_word: str, layer_idx: int,
 def extract_concept_vectors_multi_layer(model, concept_words: List[str], baseline_words: List[str],
                                         layer_indices: Sequence[int], extraction_method: str = "baseline",
                                         template: str = DEFAULT_TEMPLATE, token_idx: int = -1,
-                                        normalize: bool = False) -> Dict[int, Dict[str, torch.Tensor]]:
+                                        normalize: bool = False, sharded: bool = False) -> Dict[int, Dict[str, torch.Tensor]]:
     """All requested layers from ONE forward per prompt batch (the reference re-runs the forward for
-    every layer fraction, detect_injected_thoughts.py:1551-1561)."""
+    every layer fraction, detect_injected_thoughts.py:1551-1561).  sharded=True: a collective call of a
+    `torch.distributed` job, the prompts split over its ranks (ModelWrapper.extract_vectors_sharded_ids)."""
     if extraction_method not in ("baseline", "simple", "no_baseline"):
         raise ValueError(f"Unknown extraction method: {extraction_method}")
     if not concept_words:  # the reference's loops simply produce an empty dict
@@ -168,7 +172,8 @@ def extract_concept_vectors_multi_layer(model, concept_words: List[str], baselin
         base_prompts = [_chat_prompt(model, template.format(word="The"))]  # reference :552-553
     else:
         base_prompts = None
-    vecs = _vectors(model, concept_prompts, base_prompts, list(layer_indices), extraction_method, normalize, token_idx)
+    vecs = _vectors(model, concept_prompts, base_prompts, list(layer_indices), extraction_method, normalize, token_idx,
+                    sharded=sharded)
     return {int(layer): {w: vecs[li, ci] for ci, w in enumerate(concept_words)}
             for li, layer in enumerate(layer_indices)}
 

@@ -151,6 +151,54 @@ def test_eos_stops_rows_like_hf(wrapper):
     assert (got[:, new.shape[1]:] == 0).all()
 
 
+def test_eos_list_second_id_fires_like_hf(wrapper):
+    """generation_config.eos_token_id may be a list (Llama-3.x-Instruct: [128001, 128008, 128009], the turn ends
+    with the LAST of them): a row must stop on any id of the set, as HF `generate` stops it."""
+    enc = wrapper.tokenizer(["a b c d", "e f"], return_tensors="pt", padding=True, truncation=True)
+    width = enc["input_ids"].shape[1]
+    with torch.no_grad():
+        free = wrapper.model.generate(**enc, max_new_tokens=8, do_sample=False, pad_token_id=0)
+    fires = int(free[0, width + 2])
+    never = int(max(set(range(2, wrapper.model.config.vocab_size)) - set(free.flatten().tolist())))
+    wrapper.model.generation_config.eos_token_id = [never, fires]
+    try:
+        with torch.no_grad():
+            ref = wrapper.model.generate(**enc, max_new_tokens=8, do_sample=False, pad_token_id=0)
+        got = wrapper.steered_generate_ids(enc["input_ids"], enc["attention_mask"], None, None, None, None, None, 8)
+    finally:
+        wrapper.model.generation_config.eos_token_id = None
+    new = ref[:, width:]
+    assert torch.equal(got[:, : new.shape[1]].cpu(), new)
+    assert (got[:, new.shape[1]:] == 0).all()
+    assert (got[0, 3:] == 0).all() and int(got[0, 2]) == fires  # row 0 ended at its third token
+
+
+def test_repetition_penalty_and_generation_config_defaults_like_hf(wrapper):
+    """Qwen2.5-Instruct ships repetition_penalty 1.05 (it applies to greedy decoding too); whatever the reference's
+    `generate` call does not pass comes from the checkpoint's generation_config (reference model_utils.py:828-847)."""
+    enc = wrapper.tokenizer(["a b c d a b", "e f e f"], return_tensors="pt", padding=True, truncation=True)
+    gc_ = wrapper.model.generation_config
+    old = (gc_.repetition_penalty, gc_.top_p, gc_.top_k, gc_.do_sample, gc_.temperature)
+    gc_.repetition_penalty = 1.8
+    try:
+        with torch.no_grad():
+            ref = wrapper.model.generate(**enc, max_new_tokens=10, pad_token_id=0)
+            plain = wrapper.model.generate(**enc, max_new_tokens=10, pad_token_id=0, repetition_penalty=1.0)
+        got = wrapper.steered_generate_ids(enc["input_ids"], enc["attention_mask"], None, None, None, None, None, 10)
+        assert torch.equal(got.cpu(), ref[:, enc["input_ids"].shape[1]:])
+        assert not torch.equal(ref, plain)  # the penalty really changed the greedy path
+        gc_.top_p, gc_.top_k = 0.8, 20
+        assert wrapper._generation_settings(0.0, {"top_k": 5}) == dict(
+            do_sample=False, temperature=0.0, top_k=20, top_p=0.8, repetition_penalty=1.8)  # kwargs ignored at T=0 (:833)
+        assert wrapper._generation_settings(0.7, {"top_k": 5}) == dict(
+            do_sample=True, temperature=0.7, top_k=5, top_p=0.8, repetition_penalty=1.8)
+        gc_.do_sample, gc_.temperature = True, 0.6  # Llama-3.1-Instruct's shipped config: temperature 0 still samples
+        assert wrapper._generation_settings(0.0, {})["do_sample"] is True
+        assert wrapper._generation_settings(0.0, {})["temperature"] == 0.6
+    finally:
+        gc_.repetition_penalty, gc_.top_p, gc_.top_k, gc_.do_sample, gc_.temperature = old
+
+
 def test_hot_path_has_no_cpu_fallback(wrapper):
     v = torch.zeros(wrapper.engine.hidden)
     with pytest.raises(RuntimeError, match="no CPU path"):
@@ -173,6 +221,10 @@ def test_grid_rows_and_dedupe():
     assert len(dedup) == 4 * 50 * 30 + 50 * 15
     assert [len(c) for c in grid.chunk(rows, 64)] == [64, 64, 64, 8]
     assert rows[0] == grid.Trial("c0", 1.0, 1, "injection")
+    # numbered as the driver numbers them: control n_inj + t (:1917), forced n_inj + n_ctl + t (:1984)
+    few = grid.layer_trials(["a"], [2.0], n_injection=2, n_control=3, n_forced=2)
+    assert [(r.kind, r.trial) for r in few] == [("injection", 1), ("injection", 2), ("forced_injection", 6),
+                                                ("forced_injection", 7), ("control", 3), ("control", 4), ("control", 5)]
 
 
 def test_sweep_writers_use_the_reference_wire_format(tmp_path):
@@ -189,7 +241,7 @@ def test_sweep_writers_use_the_reference_wire_format(tmp_path):
         {"concept": "Dust", "trial": 1, "response": "nothing", "injected": False, "layer": 22, "layer_fraction": 0.7,
          "strength": 4.0, "detected": False, "trial_type": "control"},
         {"concept": "Dust", "trial": 1, "response": "about trees", "injected": True, "layer": 22, "layer_fraction": 0.7,
-         "strength": 4.0, "detected": False, "trial_type": "forced"},
+         "strength": 4.0, "detected": False, "trial_type": "forced_injection"},
     ]
     d = sweep.write_config(tmp_path / "llama_8b", 0.7, 22, 4.0, rows, temperature=1.0, max_tokens=100)
     assert d.name == "layer_0.70_strength_4.0"
@@ -197,7 +249,13 @@ def test_sweep_writers_use_the_reference_wire_format(tmp_path):
     assert set(blob) == {"results", "metrics", "n_samples"} and blob["n_samples"] == 3
     assert blob["results"][0] == rows[0]
     m = blob["metrics"]
-    assert m["detection_hit_rate"] == 1.0 and m["detection_false_alarm_rate"] == 0.0 and m["detection_accuracy"] == 1.0
+    assert m["detection_hit_rate"] == 1.0 and m["detection_false_alarm_rate"] == 0.0
+    # the three judge-only figures are written as 0 when the judge is off, as the reference driver does (:2108-2120)
+    assert m["detection_accuracy"] == 0 and m["identification_accuracy_given_claim"] == 0
+    assert m["combined_detection_and_identification_rate"] == 0
+    assert list(m)[:6] == ["detection_hit_rate", "detection_false_alarm_rate", "detection_accuracy",
+                           "identification_accuracy_given_claim", "combined_detection_and_identification_rate",
+                           "forced_identification_accuracy"]
     assert m["forced_identification_accuracy"] == 0.0 and m["layer_idx"] == 22 and m["strength"] == 4.0
     got = list(csv.DictReader(open(d / "results.csv")))
     assert len(got) == 3 and got[0]["concept"] == "Dust" and got[1]["trial_type"] == "control"
@@ -215,12 +273,16 @@ def test_sampling_distribution_matches_hf_warpers():
 
     g = torch.Generator().manual_seed(0)
     logits = torch.randn(5, 300, generator=g) * 3
-    for temp, k in ((1.0, 50), (0.7, 50), (1.3, None)):
+    from transformers.generation.logits_process import TopPLogitsWarper
+
+    for temp, k, p in ((1.0, 50, None), (0.7, 50, None), (1.3, None, None), (0.6, 50, 0.9), (1.0, 20, 0.8), (1.0, None, 0.5)):
         scores = TemperatureLogitsWarper(temp)(None, logits.clone())
         if k is not None:
             scores = TopKLogitsWarper(top_k=k)(None, scores)
+        if p is not None:
+            scores = TopPLogitsWarper(top_p=p)(None, scores)
         want = torch.softmax(scores, dim=-1)
-        got = Session.sampling_probs(logits, temp, k)
+        got = Session.sampling_probs(logits, temp, k, p)
         assert torch.allclose(got, want, atol=1e-7) and ((got > 0) == (want > 0)).all()
 
 

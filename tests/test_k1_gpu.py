@@ -152,3 +152,43 @@ def test_full_size_properties():
     # normalised rows have unit norm
     _, vn, _ = kernels.gather_meandiff(cl, bl, "baseline", True)
     assert torch.allclose(vn.float().norm(dim=-1), torch.ones(L, C, device=dev), atol=2e-2)
+
+
+@pytest.mark.parametrize("dt", ["bf16", "f16", "f32"])
+@pytest.mark.parametrize("mode", ["baseline", "simple", "raw", "posneg"])
+def test_compact_entry_bit_exact_against_oracle_and_gathered(dt, mode):
+    """ia_meandiff_compact (rows as K2's tap leaves them, [L, n, H]) against the numpy oracle and against
+    ia_gather_meandiff on the same rows: same bits, for 1..8 shares of the concept rows per (layer, tile), for
+    fewer rows than one cp.async group, for the chunked path (> 256 baseline rows) and for widths that are not
+    a multiple of the 256-column tile."""
+    from introspective_awareness_b200 import kernels
+
+    dev = _dev()
+    shapes = [(3, 5, 100, 896), (32, 50, 100, 1024), (1, 50, 100, 4096), (2, 3, 2, 136), (1, 1, 1, 4096), (2, 9, 300, 512),
+              (1, 61, 37, 3584)]
+    for k, (L, C, Nb, H) in enumerate(shapes):
+        if mode == "simple":
+            Nb = 1
+        if dt == "f16":
+            H = min(H, 896)
+        conc = residual_batch(L, C, 1, H, dt, 100 + k)[:, :, 0]
+        base = residual_batch(L, Nb, 1, H, dt, 200 + k)[:, :, 0]
+        ct, bt = to_model(conc, dt, dev), to_model(base, dt, dev)
+        for normalize in (False, True):
+            v32, vr, nr = kernels.meandiff_compact(ct, None if mode == "raw" else bt, mode, normalize)
+            g32, gr, gn = kernels.gather_meandiff([ct[l].unsqueeze(1) for l in range(L)],
+                                                  None if mode == "raw" else [bt[l].unsqueeze(1) for l in range(L)], mode, normalize)
+            torch.cuda.synchronize()
+            assert torch.equal(vr, gr) and torch.equal(v32, g32) and torch.equal(nr, gn), (dt, mode, normalize, k)
+            for l in range(L):
+                w32, wr, wn = K.meandiff(conc[l], base[l], mode, dt, normalize)
+                assert np.array_equal(vr[l].float().cpu().numpy(), wr), (dt, mode, normalize, k, l)
+                assert np.array_equal(v32[l].cpu().numpy(), w32), (dt, mode, normalize, k, l)
+                assert np.array_equal(nr[l].cpu().numpy(), wn), (dt, mode, normalize, k, l)
+        if mode == "baseline":
+            # without the norm outputs no norm pass runs and the vectors are the same
+            _, vr2, none = kernels.meandiff_compact(ct, bt, mode, False, want_f32=False, want_norm=False)
+            assert none is None and torch.equal(vr2, kernels.meandiff_compact(ct, bt, mode, False)[1])
+            s = kernels.segsum_compact(bt)
+            for l in range(L):
+                assert np.array_equal(s[l].cpu().numpy(), K.column_sum(base[l])), (dt, k, l)
