@@ -4,12 +4,13 @@
     python bench.py --impl reference --gpus N --steps K --warmup W   # reference CPU path
 
 A "step" is one pass of the hot path over one batch of synthetic input (BASELINE.json configs[1]):
-extract 50 concept vectors against 100 baseline prompts at the steering layer (two forwards + K1),
-then run 200 steered trials (50 concepts x 4 strengths, one batch, a different (concept, alpha, t0)
-per row) for 32 greedy tokens each (prompt pass + 31 cached decode steps, K2 at the layer in each).
-With N > 1 every rank is an independent replica steering its own layer of the sweep
-(configs[2], weak scaling); extraction is then prompt-sharded with one all-reduce of the fp32
-baseline sums and one all-gather of the concept rows, and the token ids are gathered to rank 0.
+extract 50 concept vectors against 100 baseline prompts at the steering layer (two forwards with K2's
+capture tap + K1), then run 200 steered trials (50 concepts x 4 strengths, one batch, a different
+(concept, alpha, t0) per row) for 32 greedy tokens each (prompt pass + 31 cached decode steps, K2 at the
+layer in each).  With N > 1 every rank is an independent replica steering its own layer of the sweep
+(configs[2], weak scaling); extraction is then prompt-sharded through the product API
+(`ModelWrapper.extract_vectors_sharded_ids`: one all-reduce of the fp32 baseline sums, one all-gather
+of the concept rows), and the token ids are gathered to rank 0.
 
 Prints ONE JSON line on rank 0.  `value` times the path with inputs resident in HBM; `e2e` times the
 same work through the public ModelWrapper-level API with pinned HOST buffers (H2D of ids / masks /
@@ -17,12 +18,19 @@ vectors / row metadata and D2H of vectors and token ids inside the timed region)
 is the fused inject+RMSNorm kernel's prompt-pass launch (the largest launch of ours in a step),
 timed live with CUDA events on its stream.  `cpu_baseline` is the reference's CPU path (the
 torch restatement in oracle/ref_hooks.py: HF generate + forward hook) on the host cores, on a
-bounded sample.  Nothing here reads /root/reference.
+bounded sample.  Outside the timed regions the line also carries: `gpu_hook_baseline` (the reference's
+own mechanism — torch-eager hooks + HF generate, one call per strength — on the same GPU and model, the
+honest "before"), `n_new_100` (the same step at the reference's default of 100 new tokens),
+`cold_shape_s` (what a batch shape the runtime has not seen costs), `strong_scaling` (configs[2] as
+written: all layers x 200 rows dealt over the ranks), at N > 1 `parity_check` (sharded vs un-sharded
+vectors, steered logits vs the hook path on every rank) and at N = 8 `other_archs` (configs[3] / [4]).
+Nothing here reads /root/reference.
 """
 
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -44,6 +52,11 @@ EXTRACT_T, EXTRACT_TMIN = 24, 8
 LAYER_FRACTION = 0.7
 METRIC = "steered trials/sec (Llama-3.1-8B)"
 UNIT = "trials/s"
+OTHER_ARCHS = ["gemma-2-9b", "qwen2.5-32b"]  # BASELINE.json configs[3] / configs[4]
+
+
+def metric_name(arch: str) -> str:
+    return METRIC if arch == ARCH else f"steered trials/sec ({arch})"
 
 
 def peak_hbm():
@@ -54,15 +67,18 @@ def peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_from_profiles(add_form: bool = False):
-    """dram read+write bytes per launch of the prompt-pass K2, from the committed ncu summary of the form
-    that was launched (plain, or with the residual add folded in)."""
-    try:
-        name = "k2_add_prefill_ncu_summary.json" if add_form else "k2_prefill_ncu_summary.json"
-        d = json.load(open(os.path.join(ROOT, "profiles", name)))
-        return float(d["dram_bytes_per_launch"])
-    except Exception:
-        return None
+def traffic_from_profiles(form: str):
+    """dram read+write bytes per launch of the prompt-pass K2, from the committed ncu --set full summary of the
+    form that was launched ("add": residual-add form, "tail": Gemma-2 block tail, "plain")."""
+    for name in {"add": ["r2_k2_add_stream_ncu_summary.json", "k2_add_prefill_ncu_summary.json"],
+                 "tail": ["r2_k2_tail_stream_ncu_summary.json"],
+                 "plain": ["r2_k2_plain_stream_ncu_summary.json", "k2_prefill_ncu_summary.json"]}[form]:
+        try:
+            d = json.load(open(os.path.join(ROOT, "profiles", name)))
+            return float(d["dram_bytes_per_launch"]), name
+        except Exception:
+            continue
+    return None, None
 
 
 class ClockSampler:
@@ -127,105 +143,262 @@ def make_workload(vocab: int, rank: int):
                 row_vec=row_vec, row_alpha=row_alpha, rows=rows)
 
 
-def run_ours(args):
-    from introspective_awareness_b200 import kernels, parallel
-    from introspective_awareness_b200.engine import SteerSpec
-    from introspective_awareness_b200.model_utils import ModelWrapper, get_layer_at_fraction
-    from introspective_awareness_b200.synthetic import build_model
-    from introspective_awareness_b200.stub_tokenizer import StubTokenizer
+class Arm:
+    """One architecture on this rank: model, wrapper, workload, and the two step functions."""
 
-    rank, world, local = parallel.init_from_env()
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py (our arm) needs a CUDA device: the hot path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    torch.manual_seed(0)
-    arch = args.arch
-    model = build_model(arch, dtype=torch.bfloat16, device=str(dev), seed=None)
-    w = ModelWrapper(arch, device=str(dev), dtype=torch.bfloat16, model=model,
-                     tokenizer=StubTokenizer(vocab_size=model.config.vocab_size), attention=args.attention)
-    eng = w.engine
-    n_layers = eng.n_layers
-    base_layer = get_layer_at_fraction(w, LAYER_FRACTION)
-    # rank r steers its own layer of the sweep (weak scaling; N=1 -> the single layer of configs[1])
-    sweep = [(base_layer + r) % n_layers for r in range(world)] if world > 1 else [base_layer]
-    my_layer = sweep[rank]
-    wl = make_workload(model.config.vocab_size, rank)
-    rows = wl["rows"]
-    on = lambda t: t.to(dev)
-    c_ids, c_mask, b_ids, b_mask = on(wl["c_ids"]), on(wl["c_mask"]), on(wl["b_ids"]), on(wl["b_mask"])
-    ids_d, mask_d = on(wl["ids"]), on(wl["mask"])
-    pads = T_PROMPT - wl["lens"]
-    t0_abs = (torch.tensor(wl["t0"]) + pads).to(torch.int32)
-    row_vec_d = torch.tensor(wl["row_vec"], dtype=torch.int32, device=dev)
-    row_alpha_d = torch.tensor(wl["row_alpha"], dtype=torch.float32, device=dev)
-    t0_d = t0_abs.to(dev)
-    # pinned host copies for the end-to-end arm
-    pin = lambda t: t.clone().pin_memory()
-    h_c_ids, h_c_mask, h_b_ids, h_b_mask = pin(wl["c_ids"]), pin(wl["c_mask"]), pin(wl["b_ids"]), pin(wl["b_mask"])
-    h_ids, h_mask = pin(wl["ids"]), pin(wl["mask"])
+    def __init__(self, arch, attention, rank, world, local):
+        from introspective_awareness_b200 import parallel
+        from introspective_awareness_b200.engine import SteerSpec
+        from introspective_awareness_b200.model_utils import ModelWrapper, get_layer_at_fraction
+        from introspective_awareness_b200.stub_tokenizer import StubTokenizer
+        from introspective_awareness_b200.synthetic import build_model
 
-    clo, chi = parallel.shard_contiguous(N_CONCEPTS, rank, world)
-    blo, bhi = parallel.shard_contiguous(N_BASE, rank, world)
-    sweep_idx = sweep.index(my_layer)
+        self.arch, self.rank, self.world = arch, rank, world
+        self.parallel, self.SteerSpec = parallel, SteerSpec
+        dev = self.dev = torch.device("cuda", local)
+        torch.manual_seed(0)
+        self.model = build_model(arch, dtype=torch.bfloat16, device=str(dev), seed=None)
+        self.w = ModelWrapper(arch, device=str(dev), dtype=torch.bfloat16, model=self.model,
+                              tokenizer=StubTokenizer(vocab_size=self.model.config.vocab_size), attention=attention)
+        eng = self.eng = self.w.engine
+        n_layers = eng.n_layers
+        base_layer = get_layer_at_fraction(self.w, LAYER_FRACTION)
+        # rank r steers its own layer of the sweep (weak scaling; N=1 -> the single layer of configs[1])
+        self.sweep = [(base_layer + r) % n_layers for r in range(world)] if world > 1 else [base_layer]
+        self.my_layer = self.sweep[rank]
+        wl = self.wl = make_workload(self.model.config.vocab_size, rank)
+        self.rows = wl["rows"]
+        on = lambda t: t.to(dev)
+        self.c_ids, self.c_mask, self.b_ids, self.b_mask = on(wl["c_ids"]), on(wl["c_mask"]), on(wl["b_ids"]), on(wl["b_mask"])
+        self.ids_d, self.mask_d = on(wl["ids"]), on(wl["mask"])
+        pads = T_PROMPT - wl["lens"]
+        self.t0_abs = (torch.tensor(wl["t0"]) + pads).to(torch.int32)
+        self.row_vec_d = torch.tensor(wl["row_vec"], dtype=torch.int32, device=dev)
+        self.row_alpha_d = torch.tensor(wl["row_alpha"], dtype=torch.float32, device=dev)
+        self.t0_d = self.t0_abs.to(dev)
+        pin = lambda t: t.clone().pin_memory()  # pinned host copies for the end-to-end arm
+        self.h_c_ids, self.h_c_mask, self.h_b_ids, self.h_b_mask = pin(wl["c_ids"]), pin(wl["c_mask"]), pin(wl["b_ids"]), pin(wl["b_mask"])
+        self.h_ids, self.h_mask = pin(wl["ids"]), pin(wl["mask"])
 
-    def extract_resident(ci=None, cm=None, bi=None, bm=None):
-        """-> [50, H] device vectors for this rank's layer (inputs default to the HBM-resident copies)."""
-        ci, cm, bi, bm = (c_ids, c_mask, b_ids, b_mask) if ci is None else (ci, cm, bi, bm)
-        if world == 1:
-            _, vr, _ = eng.extract_vectors(ci, cm, bi, bm, [my_layer], want_f32=False, want_norm=False)
-            return vr[0]
-        # prompt-sharded: this rank forwards its slice of both prompt sets, for every layer of this step
-        uniq = sorted(set(sweep))
-        cl = eng.capture_layers(ci[clo:chi], cm[clo:chi], uniq, slot=0)
-        bl = eng.capture_layers(bi[blo:bhi], bm[blo:bhi], uniq, slot=1)
-        crow, _ = kernels.gather_segsum(cl, want_rows=True)
-        _, bsum = kernels.gather_segsum(bl, want_rows=False)
-        parallel.allreduce_sum_(bsum)
-        counts = [b - a for a, b in (parallel.shard_contiguous(N_CONCEPTS, q, world) for q in range(world))]
-        crow = parallel.allgather_rows(crow, counts, dim=1)
-        _, vr, _ = kernels.meandiff_finalize(crow, bsum, N_BASE, "baseline", False, want_f32=False)
-        return vr[uniq.index(my_layer)]
+    def session(self, n_new=N_NEW):
+        return self.eng.session(self.rows, T_PROMPT, n_new, padded=True, n_vec_cap=64, vec_dtype=torch.bfloat16)
 
-    sess = eng.session(rows, T_PROMPT, N_NEW, padded=True, n_vec_cap=64, vec_dtype=torch.bfloat16)
+    def extract(self, layers, host=False):
+        """-> [len(layers), 50, H] device vectors (inputs: the HBM-resident copies, or the pinned host ones)."""
+        ci, cm, bi, bm = ((self.h_c_ids, self.h_c_mask, self.h_b_ids, self.h_b_mask) if host
+                          else (self.c_ids, self.c_mask, self.b_ids, self.b_mask))
+        if self.world == 1:
+            _, vr, _ = self.eng.extract_vectors(ci, cm, bi, bm, layers, want_f32=False, want_norm=False)
+        else:  # prompt-sharded through the product API, for every layer of this step (collective)
+            _, vr, _ = self.w.extract_vectors_sharded_ids(ci, cm, bi, bm, layers)
+        return vr
 
-    def step_resident():
-        table = extract_resident()
-        steer = SteerSpec(my_layer, table, row_vec_d, row_alpha_d, t0_d)
-        out = sess.generate(ids_d, mask_d, steer, temperature=0.0, eos_token_id=None, pad_token_id=0)
-        if world > 1:
-            parallel.gather_to_rank0(out)
+    def step_resident(self, n_new=N_NEW, layer=None, table=None):
+        if table is None:
+            uniq = sorted(set(self.sweep))
+            table = self.extract(uniq)[uniq.index(self.my_layer)]
+        steer = self.SteerSpec(self.my_layer if layer is None else layer, table, self.row_vec_d, self.row_alpha_d, self.t0_d)
+        out = self.session(n_new).generate(self.ids_d, self.mask_d, steer, temperature=0.0, eos_token_id=None, pad_token_id=0)
+        if self.world > 1:
+            self.parallel.gather_to_rank0(out)
         return out
 
-    def step_e2e():
+    def step_e2e(self):
         """Public API with host buffers: ids/masks from pinned host memory, vectors returned to the host
         (as the reference's extraction does), generation fed with host vectors, ids read back."""
-        vec_host = extract_resident(h_c_ids, h_c_mask, h_b_ids, h_b_mask).cpu()
-        out = w.steered_generate_ids(h_ids, h_mask, my_layer, vec_host, wl["row_vec"], wl["row_alpha"], wl["t0"], N_NEW,
-                                     temperature=0.0)
+        uniq = sorted(set(self.sweep))
+        vec_host = self.extract(uniq, host=True)[uniq.index(self.my_layer)].cpu()
+        wl = self.wl
+        out = self.w.steered_generate_ids(self.h_ids, self.h_mask, self.my_layer, vec_host, wl["row_vec"], wl["row_alpha"], wl["t0"],
+                                          N_NEW, temperature=0.0)
         host_ids = out.cpu()
-        if world > 1:
-            parallel.gather_to_rank0(out)
+        if self.world > 1:
+            self.parallel.gather_to_rank0(out)
         return host_ids
 
-    def barrier():
-        if world > 1:
+    def barrier(self):
+        if self.world > 1:
             torch.distributed.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        barrier()
+    def timed(self, fn, steps):
+        self.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
+        self.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=self.dev)
+        if self.world > 1:
             torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
         return float(ms.item())
 
+    def free(self):
+        self.eng._session = None
+        self.eng._extract_graphs.clear()
+        for name in ("w", "eng", "model"):
+            delattr(self, name)
+        gc.collect()
+        torch.cuda.empty_cache()
+
+
+# ---------------------------------------------------------------------------------------------
+# checks and context figures (all outside the timed regions)
+# ---------------------------------------------------------------------------------------------
+
+def parity_check(arm: Arm) -> dict:
+    """N > 1, before timing.  (a) the prompt-sharded vectors (K1a -> all-reduce -> all-gather -> K1b) against the
+    un-sharded extraction of the same prompts on this rank; (b) this rank's steered rows against the reference hook
+    path (oracle/ref_hooks.py) on a 16-row subset of its own batch: first-step logits and the greedy tokens."""
+    from oracle import ref_hooks
+
+    uniq = sorted(set(arm.sweep))
+    sharded = arm.extract(uniq)                                   # collective
+    _, whole, _ = arm.eng.extract_vectors(arm.c_ids, arm.c_mask, arm.b_ids, arm.b_mask, uniq, want_f32=False, want_norm=False)
+    a, b = sharded.float(), whole.float()
+    rel = ((a - b).norm(dim=-1) / b.norm(dim=-1)).max().item()
+    differing = (sharded != whole).float().mean().item()
+    table = whole[uniq.index(arm.my_layer)].clone()
+    wl = arm.wl
+    out = arm.w.steered_generate_ids(arm.ids_d, arm.mask_d, arm.my_layer, table, wl["row_vec"], wl["row_alpha"], wl["t0"], N_NEW,
+                                     temperature=0.0, keep_logits=True).clone()
+    ours_logits = torch.stack(arm.w.last_session.step_logits)
+    sub = list(range(16))                                          # rows 0..15 share strength STRENGTHS[0]
+    ref = ref_hooks.steered_generate(arm.model, wl["ids"][sub], wl["mask"][sub], arm.my_layer, [table[wl["row_vec"][i]].cpu() for i in sub],
+                                     STRENGTHS[0], [wl["t0"][i] for i in sub], N_NEW, want_logits=True)
+    first = (ours_logits[0, :16].cpu() - ref["logits"][0]).abs().max().item()
+    same = (out[:16].cpu() == ref["new_ids"]).all(dim=1).float().mean().item()
+    arm.w.last_session.logits_buf = None  # the timed steps run the graphs without the logits copy
+    arm.w.last_session.graphs.clear()
+    stats = torch.tensor([rel, differing, first, 1.0 - same], device=arm.dev)
+    if arm.world > 1:
+        torch.distributed.all_reduce(stats, op=torch.distributed.ReduceOp.MAX)
+    rel, differing, first, miss = stats.tolist()
+    return {"sharded_vs_unsharded_vectors_rel_l2_max": rel, "sharded_vs_unsharded_fraction_of_elements_differing": differing,
+            "first_step_logits_vs_hook_path_max_abs": first, "rows_with_identical_32_token_paths": 1.0 - miss,
+            "rows_checked_per_rank": 16, "ranks": arm.world,
+            "ok": bool(rel <= 1e-3 and first <= 2e-2),
+            "note": "max over ranks; vectors: K1a -> NCCL all-reduce / all-gather -> K1b against one un-sharded extraction; logits: "
+                    "200-row batch of ours against a 16-row hook-path batch of the same rows (north_star: <= 2e-2)"}
+
+
+def gpu_hook_baseline(arm: Arm, reps: int = 2) -> dict:
+    """The reference's own mechanism on this GPU and model: hook capture with a full-depth forward per prompt set
+    and `.cpu()` (model_utils.py:293-345), CPU vector arithmetic (vector_utils.py:541-548), then hook-steered HF
+    `generate` — one call per strength because `strength` is a scalar there (model_utils.py:692, :737), i.e. four
+    calls of 50 rows for the 200-row step."""
+    from oracle import ref_hooks
+
+    wl, model, layer = arm.wl, arm.model, arm.my_layer
+
+    def step():
+        cacts = ref_hooks.capture(model, wl["c_ids"], wl["c_mask"], layer)
+        bacts = ref_hooks.capture(model, wl["b_ids"], wl["b_mask"], layer)
+        vecs = ref_hooks.concept_vectors(cacts, bacts, "baseline")
+        for k, a in enumerate(STRENGTHS):
+            sel = list(range(k * N_CONCEPTS, (k + 1) * N_CONCEPTS))
+            ids, mask = wl["ids"][sel], wl["mask"][sel]
+            keep = int(mask.sum(1).max())  # each call is padded to its own width, as the tokenizer would
+            ref_hooks.steered_generate(model, ids[:, -keep:], mask[:, -keep:], layer, [vecs[i % N_CONCEPTS] for i in sel], a,
+                                       [wl["t0"][i] for i in sel], N_NEW)
+
+    step()
+    torch.cuda.synchronize()
+    t = time.perf_counter()
+    for _ in range(reps):
+        step()
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t) / reps
+    return {"value": arm.rows / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "calls_per_step": len(STRENGTHS), "steps_timed": reps,
+            "what": "oracle/ref_hooks.py on the same GPU and model: torch-eager forward hooks + HF generate (DynamicCache, "
+                    "no CUDA graphs, stock attention), extraction by full-depth hooked forwards + CPU arithmetic; same 200 "
+                    "rows, 32 greedy tokens, 50 + 100 extraction prompts"}
+
+
+def cold_shape(arm: Arm) -> dict:
+    """What a batch shape the runtime has not seen costs: the first `steered_generate_ids` at a new padded width
+    captures max_new_tokens - 1 step graphs; the second call of the same shape is the steady state.  Kept sessions
+    (DecoderEngine.max_sessions) and layer-independent graphs bound how often this is paid in a sweep."""
+    out = {}
+    wl = arm.wl
+    table = arm.extract([arm.my_layer])[0].clone()
+    for n_new, width in ((N_NEW, T_PROMPT - 1), (100, T_PROMPT - 2)):
+        ids, mask = wl["ids"][:, -width:].contiguous(), wl["mask"][:, -width:].contiguous()
+        t0 = [max(0, t - (T_PROMPT - width)) for t in wl["t0"]]
+        times = []
+        for _ in range(2):
+            torch.cuda.synchronize()
+            t = time.perf_counter()
+            arm.w.steered_generate_ids(ids, mask, arm.my_layer, table, wl["row_vec"], wl["row_alpha"], t0, n_new, temperature=0.0)
+            torch.cuda.synchronize()
+            times.append(time.perf_counter() - t)
+        t = time.perf_counter()  # another LAYER on the warm shape: no new graphs
+        arm.w.steered_generate_ids(ids, mask, (arm.my_layer + 1) % arm.eng.n_layers, table, wl["row_vec"], wl["row_alpha"], t0, n_new,
+                                   temperature=0.0)
+        torch.cuda.synchronize()
+        out[f"n_new_{n_new}"] = {"first_call_s": times[0], "second_call_s": times[1], "other_layer_same_shape_s": time.perf_counter() - t,
+                                 "graphs_captured": n_new - 1}
+    out["sessions_kept"] = arm.eng.max_sessions
+    return out
+
+
+def strong_scaling(arm: Arm) -> dict:
+    """configs[2] as written: ALL layers x 200 rows, the layer axis dealt round-robin over the ranks, one
+    extraction for every layer (prompt-sharded at N > 1); seconds for the whole sweep, max over ranks."""
+    n_layers = arm.eng.n_layers
+    mine = [l for l in range(n_layers) if l % arm.world == arm.rank]
+
+    def sweep():
+        vecs = arm.extract(list(range(n_layers)))
+        for l in mine:
+            arm.step_resident(layer=l, table=vecs[l])
+
+    sweep()  # warm: extraction graph of the all-layer capture
+    ms = arm.timed(sweep, 1)
+    total = n_layers * arm.rows
+    return {"layers": n_layers, "rows_total": total, "layers_per_rank": len(mine), "seconds": ms / 1e3, "value": total / (ms / 1e3),
+            "unit": UNIT, "note": "fixed total work (BASELINE configs[2]); `value` on the headline line is the weak-scaling figure"}
+
+
+def measure_other_arch(arch, args, rank, world, local) -> dict:
+    arm = Arm(arch, args.attention, rank, world, local)
+    try:
+        for _ in range(3):
+            arm.step_resident()
+        arm.eng.k2_events = []
+        ms = arm.timed(arm.step_resident, 3)
+        k2_ms = [a.elapsed_time(b) for a, b, _ in arm.eng.k2_events]
+        arm.eng.k2_events = None
+        return {"metric": metric_name(arch), "value": arm.rows * world * 3 / (ms / 1e3), "unit": UNIT, "ms_per_step": ms / 3, "steps": 3,
+                "warmup": 3, "layers": arm.sweep, "rows_per_gpu_per_step": arm.rows, "n_gpus": world,
+                "k2_prompt_pass_us": (sum(k2_ms) / len(k2_ms) * 1e3) if k2_ms else None,
+                "engine_block": "native" if arm.eng.native_block else "hf", "attention": arm.eng.attention}
+    finally:
+        arm.free()
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+
+def run_ours(args):
+    from introspective_awareness_b200 import parallel
+
+    rank, world, local = parallel.init_from_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (our arm) needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    arch = args.arch
+    arm = Arm(arch, args.attention, rank, world, local)
+    eng, rows = arm.eng, arm.rows
+
+    parity = None
+    if world > 1:
+        arm.step_resident()  # first call: builds the session and the step graphs
+        parity = parity_check(arm)
+
+    step_resident = arm.step_resident
     for _ in range(max(args.warmup, 3)):
         step_resident()
     sampler = ClockSampler(local) if rank == 0 else None
@@ -241,17 +414,16 @@ def run_ours(args):
                 torch.cuda.profiler.start()
             real_step()
 
-    ms_res = timed(step_resident, args.steps)
+    ms_res = arm.timed(step_resident, args.steps)
     launches_after = dict(eng.counters)
     if args.ncu_window:
         torch.cuda.profiler.stop()
-        step_resident = real_step
     k2_events = eng.k2_events
     eng.k2_events = None
     clocks = sampler.stop() if sampler else None
     for _ in range(2):
-        step_e2e()
-    ms_e2e = timed(step_e2e, args.steps)
+        arm.step_e2e()
+    ms_e2e = arm.timed(arm.step_e2e, args.steps)
 
     trials = rows * world * args.steps
     value = trials / (ms_res / 1e3)
@@ -263,74 +435,104 @@ def run_ours(args):
     tail = eng.fuse_gemma_tail  # Gemma-2: the block-tail variant reads mlp_out as a fifth stream and a second weight
     # Llama / Qwen2 (engine-driven block): the launch is the residual-add form — the MLP output is a fifth stream
     fifth = tail or eng.native_block
-    algo = rows * T_PROMPT * H * 2 * (5 if fifth else 4) + H * 2 * (2 if tail else 1)
+    form = "tail" if tail else ("add" if eng.native_block else "plain")
+    nvec = rows * T_PROMPT
+    algo = nvec * H * 2 * (5 if fifth else 4) + H * 2 * (2 if tail else 1)   # the table row counted as a stream
+    dram_needed = nvec * H * 2 * (4 if fifth else 3)                            # the <= 0.5 MB table stays in L2
     peak, peak_src = peak_hbm()
     k2_avg_ms = sum(k2_ms) / max(len(k2_ms), 1)
-    achieved = algo / (k2_avg_ms * 1e6) if k2_ms else None
-    # what this particular launch actually moves: only positions >= t0 read a table row and write h'
-    steered_vecs = int((T_PROMPT - t0_abs.clamp(max=T_PROMPT)).sum())
-    moved = (rows * T_PROMPT * (4 if fifth else 2) + steered_vecs * (1 if fifth else 2)) * H * 2 + H * 2
+    sec = k2_avg_ms / 1e3
+    # only positions >= t0 are steered in this launch: they alone read a table row (L2) — and in the plain form write h'
+    steered_vecs = int((T_PROMPT - arm.t0_abs.clamp(max=T_PROMPT)).sum())
+    moved = (nvec * (4 if fifth else 2) + (0 if fifth else steered_vecs)) * H * 2
+    traffic, traffic_src = traffic_from_profiles(form)
 
-    h2d = sum(t.numel() * t.element_size() for t in (h_c_ids, h_c_mask, h_b_ids, h_b_mask, h_ids, h_mask)) \
+    h2d = sum(t.numel() * t.element_size() for t in (arm.h_c_ids, arm.h_c_mask, arm.h_b_ids, arm.h_b_mask, arm.h_ids, arm.h_mask)) \
         + N_CONCEPTS * H * 2 + rows * (4 + 4 + 4)
     d2h = N_CONCEPTS * H * 2 + rows * N_NEW * 8
     # our kernels launched inside the value-timed region on this rank (counted by the engine: eager
     # launches directly, graph replays by the launches recorded at capture)
     launches_by_kernel = {k: launches_after[k] - launches_before[k] for k in launches_before}
-    if world > 1:
-        launches_by_kernel["k1_launches"] += args.steps * 4  # 2x gather_segsum + finalize + norm, called outside the engine
     launches = sum(launches_by_kernel.values())
+
+    # ---- context figures, outside the timed regions ----
+    extras = {}
+    if not args.no_extras:
+        if world == 1:
+            # the same step at the reference's default of 100 new tokens (detect_injected_thoughts.py:73)
+            for _ in range(2):
+                arm.step_resident(n_new=100)
+            ms100 = arm.timed(lambda: arm.step_resident(n_new=100), 2)
+            extras["n_new_100"] = {"value": rows * 2 / (ms100 / 1e3), "unit": UNIT, "ms_per_step": ms100 / 2, "new_tokens": 100, "steps": 2,
+                                   "warmup": 2}
+            extras["cold_shape_s"] = cold_shape(arm)
+        extras["strong_scaling"] = strong_scaling(arm)
+        if world == 1:
+            eng._session = None  # the hook path's DynamicCache and activations need the room
+            hook = gpu_hook_baseline(arm)
+            hook["ours_over_hook_path"] = value / hook["value"]
+            extras["gpu_hook_baseline"] = hook
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:  # reported at N=1 only
-        cpu = cpu_baseline_port(model, my_layer, wl, sample_rows=args.cpu_rows)
+        cpu = cpu_baseline_port(arm.model, arm.my_layer, arm.wl, sample_rows=args.cpu_rows)
+
+    sweep, fused, attention, native = arm.sweep, dict(eng._fused_checked), eng.attention, eng.native_block
+    if (world == 8 or args.other_archs) and arch == ARCH and not args.no_extras:
+        del eng
+        arm.free()
+        extras["other_archs"] = {a: measure_other_arch(a, args, rank, world, local) for a in OTHER_ARCHS}
 
     if rank == 0:
         line = {
-            "metric": METRIC if arch == ARCH else f"steered trials/sec ({arch})", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "metric": metric_name(arch), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_res / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic (random-init weights, stub-tokenised uniform ids)",
             "config": {
                 "workload": f"BASELINE configs[1]: {arch} arch, {N_CONCEPTS} concepts x {len(STRENGTHS)} strengths at one "
                             f"layer, one {rows}-row steered batch per GPU, prompt {T_PROMPT} (real {T_MIN}..{T_PROMPT}, "
                             f"left-padded), {N_NEW} greedy tokens, extraction {N_CONCEPTS}+{N_BASE} prompts per step",
-                "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": eng.attention,
-                "engine_block": "native" if eng.native_block else "hf",
-                "single_gemm_projections": {f"{k}{list(shape)}": ok for (k, shape), ok in sorted(eng._fused_checked.items())},
+                "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": attention,
+                "engine_block": "native" if native else "hf",
+                "single_gemm_projections": {f"{k}{list(shape)}": ok for (k, shape), ok in sorted(fused.items())},
                 "parallelism": "independent replicas, layer axis round-robin" if world > 1 else "single replica",
                 "l2": "inputs larger than L2: each step streams 16 GB of weights per decode step and ~1 GB of KV/activations",
             },
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "gpu_launches_by_kernel": launches_by_kernel,
-            "roofline": {"kernel": ("ia_add_inject_rmsnorm (ia::k2_tma_kernel, ADD form: residual add + inject + RMSNorm, cp.async.bulk "
-                                    "staged), prompt-pass launch" if eng.native_block else
-                                    "ia_gemma2_tail_inject_rmsnorm (ia::k2_tma_kernel, tail form: post-FFN norm + residual add + inject + "
-                                    "next RMSNorm, cp.async.bulk staged), prompt-pass launch" if tail else
-                                    "ia_inject_rmsnorm (ia::k2_tma_kernel: fused inject+RMSNorm, cp.async.bulk staged), prompt-pass launch"),
+            "roofline": {"kernel": {"add": "ia_add_inject_rmsnorm (ia::k2_stream_kernel, residual add + inject + RMSNorm; row in registers, "
+                                           "quarter-row cp.async.bulk landing slots), prompt-pass launch",
+                                    "tail": "ia_gemma2_tail_inject_rmsnorm (ia::k2_stream_kernel, post-FFN norm + residual add + inject + next "
+                                            "RMSNorm), prompt-pass launch",
+                                    "plain": "ia_inject_rmsnorm (ia::k2_stream_kernel: fused inject+RMSNorm), prompt-pass launch"}[form],
                          "bound": "hbm",
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
-                         "traffic": traffic_from_profiles(eng.native_block), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": algo, "us_per_launch": k2_avg_ms * 1e3,
-                         "steered_fraction_of_vectors": steered_vecs / (rows * T_PROMPT),
+                         # frac on the bytes DRAM has to move (3 streams plain, 4 with a branch row): the table row is an L2 hit
+                         "achieved": dram_needed / sec / 1e9 if k2_ms else None, "peak": peak, "unit": "GB/s",
+                         "frac": dram_needed / sec / 1e9 / peak if k2_ms else None,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                         "dram_necessary_bytes_per_launch": dram_needed,
+                         "survey_8d_bytes_per_launch": algo, "survey_8d_achieved": algo / sec / 1e9 if k2_ms else None,
+                         "survey_8d_frac": algo / sec / 1e9 / peak if k2_ms else None,
+                         "us_per_launch": k2_avg_ms * 1e3,
+                         "steered_fraction_of_vectors": steered_vecs / nvec,
                          "bytes_moved_per_launch": moved,
-                         "frac_of_peak_on_bytes_moved": (moved / (k2_avg_ms * 1e6) / peak) if k2_ms else None,
                          "launches_timed": len(k2_ms),
                          "share_of_step": (k2_avg_ms * len(k2_ms) / ms_res) if k2_ms else None,
                          "streams_per_vector": 5 if fifth else 4,
-                         "note": "achieved uses SURVEY 8(d)'s algorithmic bytes: residual in, table row in, h' out, y out for "
-                                 "every vector, plus the branch output in when the layer's residual add is folded into the "
-                                 "launch (streams_per_vector). In this launch only positions >= t0 "
-                                 "(steered_fraction_of_vectors) read a table row, so fewer bytes actually move "
-                                 "(bytes_moved_per_launch, frac_of_peak_on_bytes_moved); the branch output was also just "
-                                 "written by the preceding GEMM (partly L2-resident). Cold-cache, every-vector-steered "
-                                 "figures for the same shape: tools/kbench.py -> profiles/r1_kbench_ladder.jsonl; `traffic` "
-                                 "is the DRAM byte count per launch from the ncu --set full capture of the launched form "
-                                 "(profiles/k2_add_prefill_ncu_summary.json with the residual add, else "
-                                 "profiles/k2_prefill_ncu_summary.json)"},
+                         "note": "achieved / frac use the bytes DRAM must move per launch: residual in, h' out, y out for every "
+                                 "vector, plus the branch row in when the layer's residual add (or Gemma-2's block tail) is folded "
+                                 "into the launch; the concept-table row (<= 0.5 MB table) is an L2 hit and is left out. The "
+                                 "survey_8d_* figures count it as a stream, as SURVEY.md 8(d)'s formula does. In a bench step the "
+                                 "branch row was just written by the preceding GEMM and is partly L2-resident, so this live figure "
+                                 "can exceed the cold ladder's (tools/kbench.py --r2 -> profiles/r2_kbench_ladder.jsonl); `traffic` "
+                                 "is the DRAM byte count per launch of the ncu --set full capture named in traffic_source"},
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
+        if parity is not None:
+            line["parity_check"] = parity
+        line.update(extras)
         print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()
@@ -375,21 +577,36 @@ def _fast_cpu_model(arch):
     return m.eval()
 
 
-def _reference_step(model, layer, wl, rows, n_concept=2, n_base=4):
-    """The reference's own procedure on a sample: capture + mean-diff for a few prompts
-    (vector_utils.py:524-545), then hook-steered HF generate for `rows` trials (model_utils.py:687-879)."""
+SAME_CONFIG_NOTE = (
+    "not the same amount of work per step as the GPU arm: the CPU arm extracts from the real 50 + 100 prompts but decodes a "
+    "sample of {rows} of the 200 steered trials per step (one 200-row CPU step is ~400 TFLOP of prompt pass alone: hours); "
+    "trials/s is per trial on both arms, but a CPU decode step streams the same 16 GB of weights for {rows} rows as it would "
+    "for 200, so a full-batch CPU step would show more trials/s than this sample does, and a ratio against it is a "
+    "GPU-vs-CPU-sample figure. The like-for-like 'before' is gpu_hook_baseline: the reference's hook path on the same GPU.")
+
+
+def _reference_step(model, layer, wl, rows):
+    """The reference's own procedure: capture + mean-diff for the full 50 concept and 100 baseline prompts
+    (vector_utils.py:524-545; two full-depth hooked forwards), then hook-steered HF generate for a sample of
+    `rows` trials (model_utils.py:687-879)."""
     from oracle import ref_hooks
 
-    cacts = ref_hooks.capture(model, wl["c_ids"][:n_concept], wl["c_mask"][:n_concept], layer)
-    bacts = ref_hooks.capture(model, wl["b_ids"][:n_base], wl["b_mask"][:n_base], layer)
+    cacts = ref_hooks.capture(model, wl["c_ids"], wl["c_mask"], layer)
+    bacts = ref_hooks.capture(model, wl["b_ids"], wl["b_mask"], layer)
     vecs = ref_hooks.concept_vectors(cacts, bacts, "baseline")
     sel = list(range(rows))
     ids, mask = wl["ids"][sel], wl["mask"][sel]
     keep = int(mask.sum(1).max())  # re-pad the sample to its own width, as the tokenizer would
     ids, mask = ids[:, -keep:], mask[:, -keep:]
-    out = ref_hooks.steered_generate(model, ids, mask, layer, [vecs[i % n_concept] for i in sel], STRENGTHS[-1],
+    out = ref_hooks.steered_generate(model, ids, mask, layer, [vecs[wl["row_vec"][i]] for i in sel], STRENGTHS[0],
                                      [wl["t0"][i] for i in sel], N_NEW)
     return out["new_ids"]
+
+
+def _sample_text(rows, arch):
+    return (f"{rows} steered trials per step (prompt <= {T_PROMPT}, {N_NEW} greedy tokens) + extraction of the full {N_CONCEPTS} concept / "
+            f"{N_BASE} baseline prompts; reference procedure restated in oracle/ref_hooks.py (HF generate + forward hook), "
+            f"{arch} arch bf16 on the host CPU")
 
 
 def _use_all_host_threads() -> int:
@@ -403,19 +620,18 @@ def _use_all_host_threads() -> int:
     return torch.get_num_threads()
 
 
-def cpu_baseline_port(gpu_model, layer, wl, sample_rows=2):
+def cpu_baseline_port(gpu_model, layer, wl, sample_rows=8):
     threads = _use_all_host_threads()
     try:
         model = _cpu_model_from(gpu_model)
         t = time.perf_counter()
         _reference_step(model, layer, wl, sample_rows)
         dt = time.perf_counter() - t
+        arch = getattr(gpu_model.config, "model_type", "?")
         del model
         return {"value": sample_rows / dt, "unit": UNIT, "cores": threads, "kind": "port", "seconds": dt,
-                "host_cpus": os.cpu_count(),
-                "sample": f"{sample_rows} steered trials (prompt <= {T_PROMPT}, {N_NEW} greedy tokens) + extraction of "
-                          f"2 concept / 4 baseline prompts, same architecture and dtype, oracle/ref_hooks.py "
-                          f"(HF generate + forward hook) on the host CPU, one cold pass"}
+                "host_cpus": os.cpu_count(), "sample": _sample_text(sample_rows, arch) + ", one cold pass",
+                "same_config_note": SAME_CONFIG_NOTE.format(rows=sample_rows)}
     except Exception as exc:  # report, do not kill the GPU measurement
         return {"value": None, "unit": UNIT, "cores": threads, "kind": "port", "sample": f"failed: {exc!r}"}
 
@@ -424,8 +640,6 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # the CPU baseline runs once per box
-    from introspective_awareness_b200.model_utils import get_layer_at_fraction
-
     torch.manual_seed(0)
     _use_all_host_threads()
     model = _fast_cpu_model(args.arch)
@@ -441,14 +655,13 @@ def run_reference(args):
     dt = time.perf_counter() - t
     value = rows * args.steps / dt
     threads = torch.get_num_threads()
-    sample = (f"{rows} steered trials per step (prompt <= {T_PROMPT}, {N_NEW} greedy tokens) + extraction of 2 concept / "
-              f"4 baseline prompts; reference procedure restated in oracle/ref_hooks.py (HF generate + forward hook), "
-              f"{args.arch} arch bf16 on the host CPU")
+    sample = _sample_text(rows, args.arch)
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": metric_name(args.arch), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random-init weights, stub-tokenised uniform ids)",
-        "config": {"workload": f"BASELINE configs[1] on the CPU, bounded sample: {sample}", "layers": [layer]},
+        "config": {"workload": f"BASELINE configs[1] on the CPU, bounded sample: {sample}", "layers": [layer],
+                   "same_config_note": SAME_CONFIG_NOTE.format(rows=rows)},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
                          "host_cpus": os.cpu_count()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -468,6 +681,8 @@ def main():
     ap.add_argument("--attention", default="auto", choices=["auto", "gqa", "hf"],
                     help="gqa: grouped-query SDPA without repeat_kv copies; hf: the model's stock attention function")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the context figures measured outside the timed regions")
+    ap.add_argument("--other-archs", action="store_true", help="also run one short step each of configs[3] / [4] (default at --gpus 8)")
     ap.add_argument("--ncu-window", action="store_true", help="cudaProfilerStart at the last timed step (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":

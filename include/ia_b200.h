@@ -53,8 +53,10 @@ extern "C" {
 #define IA_IMPL_REGS 8   /* force the register-resident implementation */
 #define IA_IMPL_ADD_STAGED 16 /* ia_add_inject_rmsnorm: bulk-copy the branch row into the stage even in long launches */
 #define IA_IMPL_STREAM 32 /* force the streaming implementation (row in registers, quarter-row bulk-copy landing slots) */
-/* no IMPL bit: automatic — streaming for launches of >= 8192 vectors (16-bit dtypes, H in 1024/2048/3584/4096/5120),
- * TMA staging for shorter launches when a row is >= 4 KiB and the table is in the model dtype, else registers */
+/* no IMPL bit: automatic, by measurement — streaming for the two-operand forms (Gemma-2 block tail, residual add) in
+ * launches of >= 8192 vectors at H = 3584; TMA staging otherwise when a row is >= 4 KiB (always for the two-operand
+ * forms) and the table is in the model dtype; else registers.  IA_IMPL_STREAM covers 16-bit dtypes at
+ * H in 1024/2048/3584/4096/5120. */
 
 /* extraction methods (ia_gather_meandiff / ia_meandiff_finalize `mode`) */
 #define IA_MODE_BASELINE 0 /* v_c = act_c - mean_b(act_b)      vector_utils.py:541-545           */
@@ -214,8 +216,7 @@ IA_API int ia_meandiff_finalize(const void *concept_acts, int64_t n_concept, con
  * :103-109 — with no pointer table and no pass over the full residual tensors.  Same outputs, rounding points,
  * summation order and workspace (ia_meandiff_workspace_bytes) as ia_gather_meandiff; bit-identical to it on the
  * same rows.  For n_base <= 256 (the reference's 100 baseline words) this is ONE launch (+ the norm pass when
- * normalize or out_norm asks for it): a warp per (layer, 256-column tile, share of the concept rows) streams its
- * rows through a lane-private cp.async ring.
+ * normalize or out_norm asks for it).
  */
 IA_API int ia_meandiff_compact(const void *concept_acts, int64_t n_concept, const void *base_acts, int64_t n_base,
                         int64_t n_layers, int64_t H, int32_t mode, int32_t normalize, float *out_f32,

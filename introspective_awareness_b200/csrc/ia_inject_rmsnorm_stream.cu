@@ -16,9 +16,12 @@
 // per SM in every form (the staged kernel: 6 with two staged operands), each with a continuous stream
 // of bulk copies in flight instead of one row per iteration plus exposed register loads.
 //
-// Covers 16-bit model dtypes with the table in the model dtype and H/128 in {28, 32, 40} (Gemma-2-9B,
-// Llama-3.1-8B, Qwen2.5-32B: the BASELINE.json architectures) plus {8, 16} for tests; chosen
-// automatically for launches of >= 8192 vectors, forced with IA_IMPL_STREAM.
+// Covers 16-bit model dtypes with the table in the model dtype and H in {3584, 4096, 5120} (Gemma-2-9B,
+// Llama-3.1-8B, Qwen2.5-32B: the BASELINE.json architectures) plus {1024, 2048} for tests; forced with
+// IA_IMPL_STREAM.  Chosen automatically only where it measured faster than the staged kernel on B200: the
+// two-operand forms at H = 3584 in launches of >= 8192 vectors (Gemma-2 block tail 126 vs 156 us, residual add
+// 128 vs 144 us at 25 600 vectors; 0.89 of the copy bandwidth on the bytes DRAM must move).  At H = 4096 it is
+// slower than the staged kernel (row pitch a power of two: plain 143 vs 115 us) and at 5120 it spills.
 
 #include <atomic>
 

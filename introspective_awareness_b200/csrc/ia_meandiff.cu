@@ -17,7 +17,6 @@
 
 #include <algorithm>
 #include <atomic>
-#include <cstdlib>
 #include <mutex>
 
 #include "ia_common.cuh"
@@ -347,114 +346,6 @@ __global__ void __launch_bounds__(128, 4) k1_fused_kernel(RowSource<T> csrc, Row
                  warp + (int64_t)nwarps * RowBatch<T>::kRows, nwarps, o);
 }
 
-// Streaming path for n_base <= 256 (or RAW): one WARP per (layer, 256-column tile, share of the concept rows).
-// A lane owns 8 columns, as everywhere in K1, and every byte it consumes it has fetched itself: each lane
-// pushes its own 16 bytes of every row of the unit — baseline rows first, then its share of the concept rows —
-// through a private ring in shared memory with cp.async (kDepth groups of kGroupRows rows in flight), adds
-// the baseline rows in row order as they land, turns the sum into the two means, and emits the concept
-// rows as they land.  No lane ever reads another lane's bytes, so there is no barrier anywhere: a warp
-// has ~16 KB of loads in flight from its first instruction to its last row, and the warps of an SM are
-// in different phases (summing / emitting / storing) at any moment instead of marching in step.
-// Splitting the concept rows of a (layer, tile) over `nsplit` warps repeats the baseline reads (L2 hits
-// after the first warp) but not the arithmetic order: every warp adds all baseline rows in row order.
-constexpr int kGroupRows = 4;
-constexpr int kDepth = 8;  // groups in flight per lane
-
-template <typename T, bool WANT_NORM>
-__global__ void __launch_bounds__(128) k1_stream_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
-                                                        int nsplit, K1Out o) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    constexpr int kLaneBytes = 8 * (int)sizeof(T);             // 16 (or 32) bytes of a row per lane
-    constexpr int kRingRows = kGroupRows * kDepth;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
-    if (unit >= (int64_t)n_layers * o.ntiles * nsplit) return;
-    const int split = (int)(unit % nsplit);
-    const int tile = (int)((unit / nsplit) % o.ntiles);
-    const int layer = (int)(unit / ((int64_t)nsplit * o.ntiles));
-    const int col = tile * kTileCols + lane * 8;
-    const bool active = col < H;
-    // ring[row slot][lane]: lane-private 16/32-byte cells
-    unsigned char *ring = smem + ((size_t)warp * kRingRows * 32 + lane) * kLaneBytes;
-    const int64_t nb = raw ? 0 : bsrc.n;
-    const int64_t n_mine = csrc.n > split ? (csrc.n - split + nsplit - 1) / nsplit : 0;
-    const int64_t total = nb + n_mine;
-    const int64_t ngroups = (total + kGroupRows - 1) / kGroupRows;
-
-    auto issue_group = [&](int64_t g) {
-        if (active && g < ngroups) {
-#pragma unroll
-            for (int u = 0; u < kGroupRows; ++u) {
-                const int64_t q = g * kGroupRows + u;
-                if (q < total) {
-                    const T *src = q < nb ? bsrc.at(layer, q, H) : csrc.at(layer, split + (q - nb) * nsplit, H);
-                    unsigned char *d = ring + (size_t)((g % kDepth) * kGroupRows + u) * 32 * kLaneBytes;
-                    cp_async16(d, src + col);
-                    if (sizeof(T) == 4) cp_async16(d + 16, src + col + 4);
-                }
-            }
-        }
-        asm volatile("cp.async.commit_group;\n" ::);  // always: the group count per iteration stays fixed
-    };
-#pragma unroll
-    for (int g = 0; g < kDepth; ++g) issue_group(g);
-
-    float acc[8], mean32[8], meanr[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { acc[i] = 0.f; mean32[i] = 0.f; meanr[i] = 0.f; }
-    bool have_mean = nb == 0;
-    for (int64_t g = 0; g < ngroups; ++g) {
-        asm volatile("cp.async.wait_group %0;\n" ::"n"(kDepth - 1) : "memory");  // group g has landed
-#pragma unroll
-        for (int u = 0; u < kGroupRows; ++u) {
-            const int64_t q = g * kGroupRows + u;
-            if (q >= total) break;
-            float a[8];
-            if (active) {
-                lds8<T>(ring + (size_t)((g % kDepth) * kGroupRows + u) * 32 * kLaneBytes, a);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) a[i] = 0.f;
-            }
-            if (q < nb) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], a[i]);
-                continue;
-            }
-            if (!have_mean) {
-                const float n = (float)nb;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    mean32[i] = active ? __fdiv_rn(acc[i], n) : 0.f;
-                    meanr[i] = Elt<T>::rd(mean32[i]);
-                }
-                have_mean = true;
-            }
-            const int64_t c = split + (q - nb) * nsplit;
-            float v32[8], vr[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                v32[i] = raw ? a[i] : __fsub_rn(a[i], mean32[i]);
-                vr[i] = raw ? a[i] : Elt<T>::rd(__fsub_rn(a[i], meanr[i]));
-            }
-            const int64_t orow = (int64_t)layer * csrc.n + c;
-            if (active) {
-                if (o.out_f32) store8<float>(o.out_f32 + orow * H + col, v32);
-                store8<T>(static_cast<T *>(o.out_rounded) + orow * H + col, vr);
-            }
-            if (WANT_NORM) {
-                const float p32 = sq8_warp(v32);
-                const float pr = sq8_warp(vr);
-                if (lane == 0) {
-                    o.part32[orow * o.ntiles + tile] = p32;
-                    o.partr[orow * o.ntiles + tile] = pr;
-                }
-            }
-        }
-        issue_group(g + kDepth);  // refills the cells this lane has just read
-    }
-}
-
 // Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.  Small CTAs
 // (4 warps, 32 KB of staging) so that ~7 are resident per SM: a CTA's start-up and drain (pointer
 // table -> first rows -> last adds -> store), during which it has no loads in flight, is then
@@ -696,42 +587,17 @@ static int meandiff_t(const RowSource<T> &csrc, const RowSource<T> &bsrc, int L,
     const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : nc;
     if (mode != IA_MODE_POSNEG && (mode == IA_MODE_RAW || nb <= kChunkRows)) {
         const bool want_norm = normalize || out_norm;
-        static const bool use_cta_kernel = std::getenv("IA_K1_CTA") != nullptr;  // A/B switch for tools/kbench.py
-        cudaError_t e;
-        if (!use_cta_kernel) {
-            // streaming kernel: enough warps to fill the machine (~10 per SM), each a (layer, tile, share of
-            // the concept rows) unit
-            const int64_t units = (int64_t)L * ntiles;
-            int nsplit = (int)std::min<int64_t>(std::max<int64_t>(1, (148 * 10 + units - 1) / units), std::max<int64_t>(1, std::min<int64_t>(nc, 8)));
-            const int lane_bytes = 8 * (int)sizeof(T);
-            const int smem = 4 * kGroupRows * kDepth * 32 * lane_bytes;
-            const int64_t warps = units * nsplit;
-            int rc;
-            if (want_norm) {
-                static std::atomic<bool> done[64];
-                rc = opt_in_smem(k1_stream_kernel<T, true>, done, smem);
-                if (rc) return rc;
-                k1_stream_kernel<T, true><<<(unsigned)((warps + 3) / 4), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, nsplit, o);
-            } else {
-                static std::atomic<bool> done[64];
-                rc = opt_in_smem(k1_stream_kernel<T, false>, done, smem);
-                if (rc) return rc;
-                k1_stream_kernel<T, false><<<(unsigned)((warps + 3) / 4), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, nsplit, o);
-            }
-            e = cudaGetLastError();
-        } else {
-            // all baseline rows in one pass when they fit half the staging budget each way (two halves of
-            // `stage_rows` rows), otherwise two alternating half-size passes
-            const int row_bytes = kTileCols * (int)sizeof(T);
-            const int half_rows = kStageBytes / 2 / row_bytes;
-            const int stage_rows = nb <= 2 * half_rows ? (int)std::max<int64_t>(nb, 1) : half_rows;
-            const int smem = kMeanBytes + (mode == IA_MODE_RAW ? 0 : (nb <= 2 * half_rows ? stage_rows : 2 * stage_rows) * row_bytes);
-            static std::atomic<bool> done[64];
-            const int rc = opt_in_smem(k1_fused_kernel<T>, done, kMeanBytes + kStageBytes);
-            if (rc) return rc;
-            k1_fused_kernel<T><<<(unsigned)(L * ntiles), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, o);
-            e = cudaGetLastError();
-        }
+        // all baseline rows in one pass when they fit half the staging budget each way (two halves of
+        // `stage_rows` rows), otherwise two alternating half-size passes
+        const int row_bytes = kTileCols * (int)sizeof(T);
+        const int half_rows = kStageBytes / 2 / row_bytes;
+        const int stage_rows = nb <= 2 * half_rows ? (int)std::max<int64_t>(nb, 1) : half_rows;
+        const int smem = kMeanBytes + (mode == IA_MODE_RAW ? 0 : (nb <= 2 * half_rows ? stage_rows : 2 * stage_rows) * row_bytes);
+        static std::atomic<bool> done[64];
+        const int rc = opt_in_smem(k1_fused_kernel<T>, done, kMeanBytes + kStageBytes);
+        if (rc) return rc;
+        k1_fused_kernel<T><<<(unsigned)(L * ntiles), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, o);
+        cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         if (!want_norm) return 0;  // nobody reads the norms
         const int64_t rows = (int64_t)L * n_out;

@@ -137,11 +137,19 @@ class SteerSpec:
     row_vec[b] < 0 marks a control row; row_t0 None steers every position
     (reference model_utils.py:798-802)."""
 
-    layer_idx: int
+    layer_idx: Optional[int]          # None: `row_vec` is [n_layers, B], one row of vector indices per decoder layer
     vtable: torch.Tensor              # [n_vec, H] model dtype or fp32, on the device
-    row_vec: torch.Tensor             # [B] int32
+    row_vec: torch.Tensor             # [B] int32 (or [n_layers, B], see layer_idx)
     row_alpha: torch.Tensor           # [B] float32
     row_t0: Optional[torch.Tensor]    # [B] int32 absolute (pad-shifted) start, or None
+
+    def at(self, i: int) -> Optional["SteerSpec"]:
+        """The steering that applies after decoder layer i, or None.  With per-layer index rows (the decode
+        graphs: every layer's block-tail K2 launch reads its own row of indices, -1 = leave the row alone, so
+        WHICH layer is steered is data, not part of the captured graph) every layer gets a spec."""
+        if self.layer_idx is None:
+            return SteerSpec(i, self.vtable, self.row_vec[i], self.row_alpha, self.row_t0)
+        return self if self.layer_idx == i else None
 
 
 class StaticKV:
@@ -220,6 +228,8 @@ class DecoderEngine:
         self._rope_module = _sys.modules[type(first.self_attn).__module__]
         self.fused_rope = self.device.type == "cuda"
         self._extract_graphs: Dict[tuple, tuple] = {}
+        self._sessions: Dict[tuple, "Session"] = {}   # insertion order = least recently used first
+        self.max_sessions = 3
         if attention == "auto":
             attention = "gqa" if self.device.type == "cuda" else "hf"
         self.attention = attention
@@ -365,7 +375,8 @@ class DecoderEngine:
             normed_in = None
             attn, _ = layer.self_attn(hidden_states=x, position_embeddings=pos_emb,
                                       attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
-            steer_here = steer is not None and steer.layer_idx == i
+            st = steer.at(i) if steer is not None else None
+            steer_here = st is not None
             if self.is_gemma2:
                 h = residual + self.norm(layer.post_attention_layernorm, attn)
                 residual = h
@@ -378,9 +389,9 @@ class DecoderEngine:
                         ev[0].record()
                     y = kernels.gemma2_tail_inject_rmsnorm(
                         m.contiguous(), residual, layer.post_feedforward_layernorm.weight, nxt.weight, self.eps,
-                        vtable=steer.vtable, row_vec=steer.row_vec, row_alpha=steer.row_alpha,
-                        row_t0=None if decode else steer.row_t0, pos0=pos0,
-                        steer_all=decode or steer.row_t0 is None)
+                        vtable=st.vtable, row_vec=st.row_vec, row_alpha=st.row_alpha,
+                        row_t0=None if decode else st.row_t0, pos0=pos0,
+                        steer_all=decode or st.row_t0 is None)
                     if ev is not None:
                         ev[1].record()
                         self.k2_events.append((ev[0], ev[1], residual.numel() * residual.element_size()))
@@ -406,10 +417,10 @@ class DecoderEngine:
                 if self.k2_events is not None and not decode:
                     ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
                     ev[0].record()
-                y = kernels.inject_rmsnorm(h, nxt.weight, self.eps, self.variant, vtable=steer.vtable,
-                                           row_vec=steer.row_vec, row_alpha=steer.row_alpha,
-                                           row_t0=None if decode else steer.row_t0, pos0=pos0,
-                                           steer_all=decode or steer.row_t0 is None)
+                y = kernels.inject_rmsnorm(h, nxt.weight, self.eps, self.variant, vtable=st.vtable,
+                                           row_vec=st.row_vec, row_alpha=st.row_alpha,
+                                           row_t0=None if decode else st.row_t0, pos0=pos0,
+                                           steer_all=decode or st.row_t0 is None)
                 if ev is not None:
                     ev[1].record()
                     self.k2_events.append((ev[0], ev[1], h.numel() * h.element_size()))
@@ -550,7 +561,7 @@ class DecoderEngine:
                                       attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
             x = self._gemma_tail(attn, h, layer.post_attention_layernorm.weight, layer.pre_feedforward_layernorm.weight)
             m = layer.mlp(x)
-            st = steer if (steer is not None and steer.layer_idx == i) else None
+            st = steer.at(i) if steer is not None else None
             nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
             if i == last and stop_after is not None and st is None and i in captured:
                 # nothing downstream: finish the captured rows only (B vectors instead of B*T), in the capture buffer
@@ -580,7 +591,7 @@ class DecoderEngine:
             attn = self._attn_native(layer, i, x, pos_emb, masks[self._layer_kind(i)], cache)
             x = self._k2(h, layer.post_attention_layernorm.weight, add=attn)
             m = self._mlp_native(layer, i, x)
-            st = steer if (steer is not None and steer.layer_idx == i) else None
+            st = steer.at(i) if steer is not None else None
             if i == last and stop_after is not None and st is None:
                 # nothing reads a normed output after the last requested layer: finish the captured rows only
                 if i in captured:
@@ -705,15 +716,42 @@ class DecoderEngine:
     # -- generation ---------------------------------------------------------------------------
     def session(self, batch: int, prompt_len: int, max_new_tokens: int, padded: bool, n_vec_cap: int = 64,
                 vec_dtype: Optional[torch.dtype] = None, use_graphs: Optional[bool] = None) -> "Session":
+        """The static buffers and step graphs for one batch shape.  A sweep alternates between a few shapes (the
+        padded width moves by a token when trial numbers gain a digit; the last batch of a layer is shorter), and a
+        new shape costs max_new_tokens - 1 graph captures, so the last `max_sessions` shapes are kept, least
+        recently used first out — fewer when their KV caches would not fit next to a new one."""
         key = (batch, prompt_len, max_new_tokens, padded, n_vec_cap, vec_dtype)
-        cur = getattr(self, "_session", None)
-        if cur is not None and cur.key == key:
-            return cur
-        self._session = None  # free the old KV cache / graphs before allocating
+        sess = self._sessions.pop(key, None)
+        if sess is None:
+            need = 2 * self.n_layers * batch * self.n_kv * (prompt_len + max_new_tokens) * self.head_dim * self.model.dtype.itemsize
+            while self._sessions and (len(self._sessions) >= self.max_sessions or not self._fits(need)):
+                self._sessions.pop(next(iter(self._sessions)))  # oldest first
+                if self.device.type == "cuda":
+                    gc.collect()
+                    torch.cuda.empty_cache()
+            sess = Session(self, key, use_graphs)
+        self._sessions[key] = sess  # most recently used last
+        return sess
+
+    def _fits(self, kv_bytes: int) -> bool:
+        if self.device.type != "cuda":
+            return True
+        free, _ = torch.cuda.mem_get_info(self.device)
+        return free + torch.cuda.memory_reserved(self.device) - torch.cuda.memory_allocated(self.device) > 2 * kv_bytes
+
+    @property
+    def _session(self):
+        """The most recently used session (None when there is none); assigning None drops every kept session."""
+        return next(reversed(self._sessions.values())) if self._sessions else None
+
+    @_session.setter
+    def _session(self, value):
+        if value is not None:
+            raise ValueError("sessions are created by DecoderEngine.session()")
+        self._sessions.clear()
         if self.device.type == "cuda":
+            gc.collect()
             torch.cuda.empty_cache()
-        self._session = Session(self, key, use_graphs)
-        return self._session
 
 
 class Session:
@@ -733,6 +771,8 @@ class Session:
         self.unfinished = torch.ones(b, dtype=torch.bool, device=dev)
         self.vtable = torch.zeros(n_vec_cap, eng.hidden, dtype=vec_dtype or eng.dtype, device=dev)
         self.row_vec = torch.full((b,), -1, dtype=torch.int32, device=dev)
+        # decode graphs: one row of vector indices per decoder layer, -1 everywhere except the steered layer
+        self.row_vec_layers = torch.full((eng.n_layers, b), -1, dtype=torch.int32, device=dev)
         self.row_alpha = torch.zeros(b, dtype=torch.float32, device=dev)
         self.row_t0 = torch.zeros(b, dtype=torch.int32, device=dev)
         self.use_graphs = (dev.type == "cuda") if use_graphs is None else use_graphs
@@ -868,6 +908,8 @@ class Session:
                 self.row_t0.copy_(steer.row_t0, non_blocking=True)
             st = SteerSpec(steer.layer_idx, self.vtable, self.row_vec, self.row_alpha,
                            self.row_t0 if steer.row_t0 is not None else None)
+            self.row_vec_layers.fill_(-1)
+            self.row_vec_layers[steer.layer_idx].copy_(self.row_vec)
         self.key_valid[:, : self.T].copy_(mask.bool())
         self.unfinished.fill_(True)
 
@@ -892,14 +934,17 @@ class Session:
                 self.logits_buf = torch.empty(self.B, lg.shape[-1], dtype=lg.dtype, device=eng.device)
                 self.graphs.clear()
             graphs = None
+            # decode steps steer every position of a steered row, whatever t0 was; the steered LAYER is data (the
+            # per-layer index rows), so one set of step graphs serves every layer of a sweep
+            st_dec = None if st is None else SteerSpec(None, self.vtable, self.row_vec_layers, self.row_alpha, None)
             if self.use_graphs:
-                gkey = (None if st is None else (st.layer_idx, st.row_t0 is None), greedy, eos_token_id, pad_token_id,
-                        self.logits_buf is not None, penalty if greedy else 1.0)
+                gkey = (st is not None, greedy, eos_token_id, pad_token_id, self.logits_buf is not None,
+                        penalty if greedy else 1.0)
                 if gkey not in self.graphs:
                     # capturing runs warm-up steps that scribble on the state: save and restore it
                     state = [self.tok, self.posid, self.out_ids, self.unfinished] + ([self.hist] if self.hist is not None else [])
                     keep = [t.clone() for t in state]
-                    graphs = self._ensure_graphs(gkey, st, greedy, eos_token_id, pad_token_id, penalty)
+                    graphs = self._ensure_graphs(gkey, st_dec, greedy, eos_token_id, pad_token_id, penalty)
                     for dst, src in zip(state, keep):
                         dst.copy_(src)
                 graphs = self.graphs[gkey]
@@ -909,7 +954,7 @@ class Session:
                     for k, v in graphs[s - 1].ia_launches.items():
                         eng.counters[k] += v
                 else:
-                    self._step(s, st, greedy, eos_token_id, pad_token_id, penalty)
+                    self._step(s, st_dec, greedy, eos_token_id, pad_token_id, penalty)
                 if keep_logits:
                     self.step_logits.append(self.logits_buf.float().clone())
                 if not greedy:

@@ -24,7 +24,7 @@ def _case(dev, L, C, Nb, H, T, seed, dtype=torch.bfloat16):
     return conc, base
 
 
-def _run_static(lib, conc, base, mode, normalize, kernels):
+def _run_static(lib, conc, base, mode, normalize, kernels, check_device_free=False):
     """All buffers are made here, by the caller; the call under test receives pointers only."""
     dev = conc[0].device
     L, (C, T, H) = len(conc), conc[0].shape
@@ -36,12 +36,17 @@ def _run_static(lib, conc, base, mode, normalize, kernels):
     outn = torch.full((L, n_out), float("nan"), dtype=torch.float32, device=dev)
     torch.cuda.synchronize()
     before = torch.cuda.memory_allocated(dev)
+    free_before, _ = torch.cuda.mem_get_info(dev)  # cudaMemGetInfo: sees ANY device allocation, the library's own included
     rc = lib.ia_gather_meandiff_static(cptr.data_ptr(), T, 0, 0, C, bptr.data_ptr(), T, 0, 0, Nb, L, H,
                                        kernels.MODES[mode], int(normalize), out32.data_ptr(), outr.data_ptr(),
                                        outn.data_ptr(), kernels._dt(conc[0]), torch.cuda.current_stream().cuda_stream)
     assert rc == 0, lib.ia_error_string(rc)
     assert torch.cuda.memory_allocated(dev) == before  # the call went through no torch allocation
     torch.cuda.synchronize()
+    if check_device_free:
+        # ... and through no cudaMalloc of its own: the device's free memory is what it was (checked on calls after
+        # the first one on this device, whose set-up may make the driver load the kernels' module)
+        assert torch.cuda.mem_get_info(dev)[0] == free_before
     return out32, outr, outn
 
 
@@ -65,7 +70,7 @@ def test_static_scratch_entry_point_matches_workspace_entry_point_twice():
             assert not torch.isnan(a.float()).any(), name
             assert torch.equal(a, b), (shape, mode, name)
     # the same request again: a repeat call over the used scratch gives the same bits
-    again = _run_static(lib, conc, base, mode, normalize, kernels)
+    again = _run_static(lib, conc, base, mode, normalize, kernels, check_device_free=True)
     assert all(torch.equal(a, b) for a, b in zip(again, want))
 
 

@@ -61,7 +61,7 @@ def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16, add=F
     e = h.element_size()
 
     lib = _lib.load()
-    flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS}[impl]
+    flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS, "stream": _lib.IA_IMPL_STREAM}[impl]
     if add_staged:
         flags |= _lib.IA_IMPL_ADD_STAGED
     args = (h.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(), t0.data_ptr(),
@@ -79,8 +79,9 @@ def bench_k2(rows, T, H, variant, impl, reps, flush, dtype=torch.bfloat16, add=F
 
     ms = time_launch(fn, reps, flush)
     algo = rows * T * H * e * (5 if add else 4) + H * e
+    dram = rows * T * H * e * (4 if add else 3)  # the table row is an L2 hit: bytes DRAM must move
     return dict(kernel="k2_add_inject_rmsnorm" if add else "k2_inject_rmsnorm", impl=impl, variant=variant, rows=rows, T=T,
-                H=H, bytes=algo, us=ms * 1e3, gbs=algo / ms / 1e6)
+                H=H, bytes=algo, dram_bytes=dram, us=ms * 1e3, gbs=algo / ms / 1e6, dram_gbs=dram / ms / 1e6)
 
 
 def bench_tail(rows, H, impl, reps, flush, dtype=torch.bfloat16):
@@ -96,7 +97,7 @@ def bench_tail(rows, H, impl, reps, flush, dtype=torch.bfloat16):
     alpha = torch.full((rows,), 4.0, device=dev)
     t0 = torch.zeros(rows, device=dev, dtype=torch.int32)
     lib = _lib.load()
-    flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS}[impl]
+    flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS, "stream": _lib.IA_IMPL_STREAM}[impl]
     args = (mlp.data_ptr(), res.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(), t0.data_ptr(),
             w.data_ptr(), w.data_ptr(), 1e-6, rows, 1, H, 0, kernels._dt(res), kernels._dt(vt), flags,
             torch.cuda.current_stream().cuda_stream)
@@ -107,7 +108,42 @@ def bench_tail(rows, H, impl, reps, flush, dtype=torch.bfloat16):
 
     ms = time_launch(fn, reps, flush)
     algo = rows * H * res.element_size() * 5 + 2 * H * res.element_size()
-    return dict(kernel="k2_gemma2_tail", impl=impl, rows=rows, T=1, H=H, bytes=algo, us=ms * 1e3, gbs=algo / ms / 1e6)
+    dram = rows * H * res.element_size() * 4
+    return dict(kernel="k2_gemma2_tail", impl=impl, rows=rows, T=1, H=H, bytes=algo, dram_bytes=dram, us=ms * 1e3,
+                gbs=algo / ms / 1e6, dram_gbs=dram / ms / 1e6)
+
+
+def bench_copy(nbytes, reps, flush):
+    """torch's device copy moving `nbytes` in total (half read, half written), timed the same way: what the copy
+    that defines MEASURED_PEAKS.json's hbm_gbs achieves at THIS size (launch ramp and tail included)."""
+    n = nbytes // 4  # bf16 elements each way
+    a = torch.empty(n, dtype=torch.bfloat16, device="cuda:0").normal_()
+    b = torch.empty_like(a)
+    ms = time_launch(lambda: b.copy_(a), reps, flush)
+    return dict(kernel="torch_copy", bytes=2 * n * 2, us=ms * 1e3, gbs=2 * n * 2 / ms / 1e6)
+
+
+def bench_k1_compact(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16, want_norm=False):
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(0)
+    ca = torch.randn(n_layers, C, H, device=dev, generator=g).to(dtype)
+    ba = torch.randn(n_layers, Nb, H, device=dev, generator=g).to(dtype)
+    e = ca.element_size()
+    ws = torch.empty(kernels.workspace_bytes(n_layers, C, Nb, H) + 256, dtype=torch.uint8, device=dev)
+    out_r = torch.empty(n_layers, C, H, dtype=dtype, device=dev)
+    out_n = torch.empty(n_layers, C, dtype=torch.float32, device=dev)
+    lib = _lib.load()
+    args = (ca.data_ptr(), C, ba.data_ptr(), Nb, n_layers, H, _lib.IA_MODE_BASELINE, 0, 0, out_r.data_ptr(),
+            0 if not want_norm else out_n.data_ptr(), ws.data_ptr(), ws.numel(), kernels._dt(ca), torch.cuda.current_stream().cuda_stream)
+
+    def fn():
+        rc = lib.ia_meandiff_compact(*args)
+        assert rc == 0, rc
+
+    ms = time_launch(fn, reps, flush)
+    algo = n_layers * ((C + Nb) * H * e + C * H * e)
+    return dict(kernel="k1_meandiff_compact", n_layers=n_layers, C=C, Nb=Nb,
+                H=H, norm_pass=want_norm, bytes=algo, us=ms * 1e3, gbs=algo / ms / 1e6)
 
 
 def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16, want_norm=False):
@@ -140,7 +176,11 @@ def bench_k1(n_layers, C, Nb, H, reps, flush, dtype=torch.bfloat16, want_norm=Fa
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
-    ap.add_argument("--impl", default="auto", choices=["auto", "regs", "tma"])
+    ap.add_argument("--impl", default="auto", choices=["auto", "regs", "tma", "stream"])
+    ap.add_argument("--r2", action="store_true", help="round-2 ladder: streaming vs staged K2 (plain / add / tail), torch copy at "
+                                                      "the same sizes, compact K1")
+    ap.add_argument("--only-form", default="plain", choices=["plain", "add", "tail"], help="with --only-rows")
+    ap.add_argument("--only-h", type=int, default=4096, help="with --only-rows")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only-rows", type=int, default=0, help="run a single cold K2 shape (for ncu --set full)")
     ap.add_argument("--only-k1", action="store_true", help="run only the K1 ladder")
@@ -149,8 +189,36 @@ def main():
     args = ap.parse_args()
     peak, src = peak_gbs()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda:0")
+    if args.r2:
+        def emit(r, **extra):
+            r.update(cache="cold", frac=r["gbs"] / peak, peak=peak, peak_src=src, **extra)
+            if "dram_gbs" in r:
+                r["dram_frac"] = r["dram_gbs"] / peak
+            print(json.dumps(r), flush=True)
+
+        for rows in (() if args.only_k1 else (3000, 8192, 25600, 262144)):
+            for H in (4096, 5120, 3584):
+                for impl in ("stream", "tma"):
+                    emit(bench_k2(rows, 1, H, "gemma" if H == 3584 else "llama", impl, args.reps, flush))
+                    if H != 3584:
+                        emit(bench_k2(rows, 1, H, "llama", impl, args.reps, flush, add=True))
+                    else:
+                        emit(bench_tail(rows, H, impl, args.reps, flush))
+            for nbytes in (rows * 4096 * 2 * 3, rows * 4096 * 2 * 4):
+                emit(bench_copy(nbytes, args.reps, flush))
+        for (L, C, Nb) in [(1, 50, 100), (32, 50, 100), (64, 50, 100), (1, 50, 16334), (1, 50, 262094)]:
+            for want_norm in (False, True):
+                emit(bench_k1_compact(L, C, Nb, 4096, args.reps, flush, want_norm=want_norm))
+            emit(bench_k1(L, C, Nb, 4096, args.reps, flush))
+        return
+    if args.only_rows and args.only_form == "tail":
+        r = bench_tail(args.only_rows, args.only_h, args.impl, args.reps, flush)
+        r.update(cache="cold", frac=r["gbs"] / peak, peak=peak, peak_src=src)
+        print(json.dumps(r), flush=True)
+        return
     if args.only_rows:
-        r = bench_k2(args.only_rows, 1, 4096, "llama", args.impl, args.reps, flush, add=args.add, add_staged=args.add_staged)
+        args.add = args.add or args.only_form == "add"
+        r = bench_k2(args.only_rows, 1, args.only_h, "llama", args.impl, args.reps, flush, add=args.add, add_staged=args.add_staged)
         r["add_staged"] = args.add_staged
         r.update(cache="cold", frac=r["gbs"] / peak, peak=peak, peak_src=src)
         print(json.dumps(r), flush=True)
