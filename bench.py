@@ -70,9 +70,9 @@ def peak_hbm():
 def traffic_from_profiles(form: str):
     """dram read+write bytes per launch of the prompt-pass K2, from the committed ncu --set full summary of the
     form that was launched ("add": residual-add form, "tail": Gemma-2 block tail, "plain")."""
-    for name in {"add": ["r2_k2_add_stream_ncu_summary.json", "k2_add_prefill_ncu_summary.json"],
-                 "tail": ["r2_k2_tail_stream_ncu_summary.json"],
-                 "plain": ["r2_k2_plain_stream_ncu_summary.json", "k2_prefill_ncu_summary.json"]}[form]:
+    for name in {"add": ["r2_k2_add_tma_4096_ncu_summary.json", "k2_add_prefill_ncu_summary.json"],
+                 "tail": ["r2_k2_tail_stream_3584_ncu_summary.json"],
+                 "plain": ["r2_k2_plain_tma_4096_ncu_summary.json", "k2_prefill_ncu_summary.json"]}[form]:
         try:
             d = json.load(open(os.path.join(ROOT, "profiles", name)))
             return float(d["dram_bytes_per_launch"]), name
@@ -446,6 +446,9 @@ def run_ours(args):
     steered_vecs = int((T_PROMPT - arm.t0_abs.clamp(max=T_PROMPT)).sum())
     moved = (nvec * (4 if fifth else 2) + (0 if fifth else steered_vecs)) * H * 2
     traffic, traffic_src = traffic_from_profiles(form)
+    # which implementation the library picks for this launch (csrc/ia_inject_rmsnorm.cu, k2_entry)
+    impl_name = ("ia::k2_stream_kernel: row in registers, quarter-row cp.async.bulk landing slots" if form != "plain" and H == 3584
+                 else "ia::k2_tma_kernel: cp.async.bulk staged rows")
 
     h2d = sum(t.numel() * t.element_size() for t in (arm.h_c_ids, arm.h_c_mask, arm.h_b_ids, arm.h_b_mask, arm.h_ids, arm.h_mask)) \
         + N_CONCEPTS * H * 2 + rows * (4 + 4 + 4)
@@ -501,11 +504,10 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "gpu_launches_by_kernel": launches_by_kernel,
-            "roofline": {"kernel": {"add": "ia_add_inject_rmsnorm (ia::k2_stream_kernel, residual add + inject + RMSNorm; row in registers, "
-                                           "quarter-row cp.async.bulk landing slots), prompt-pass launch",
-                                    "tail": "ia_gemma2_tail_inject_rmsnorm (ia::k2_stream_kernel, post-FFN norm + residual add + inject + next "
-                                            "RMSNorm), prompt-pass launch",
-                                    "plain": "ia_inject_rmsnorm (ia::k2_stream_kernel: fused inject+RMSNorm), prompt-pass launch"}[form],
+            "roofline": {"kernel": {"add": "ia_add_inject_rmsnorm (residual add + inject + RMSNorm; " + impl_name + "), prompt-pass launch",
+                                    "tail": "ia_gemma2_tail_inject_rmsnorm (post-FFN norm + residual add + inject + next RMSNorm; "
+                                            + impl_name + "), prompt-pass launch",
+                                    "plain": "ia_inject_rmsnorm (fused inject+RMSNorm; " + impl_name + "), prompt-pass launch"}[form],
                          "bound": "hbm",
                          # frac on the bytes DRAM has to move (3 streams plain, 4 with a branch row): the table row is an L2 hit
                          "achieved": dram_needed / sec / 1e9 if k2_ms else None, "peak": peak, "unit": "GB/s",

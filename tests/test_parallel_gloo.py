@@ -81,6 +81,20 @@ def _worker(rank, world, port, out_dir):
     raw = parallel.extract_vectors_sharded(capture_rows_and_sum, finalize, C, Nb, "no_baseline", False)
     assert np.array_equal(raw, conc)
     np.save(os.path.join(out_dir, f"vec{rank}.npy"), got)
+
+    # the sweep through the product API on two ranks: layer fractions dealt round-robin, every rank writes the
+    # files of its own configurations, result rows gathered to rank 0
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_reference_sweep_dropin import ScriptedModel
+    from introspective_awareness_b200 import sweep, vector_utils as vu
+
+    model = ScriptedModel(chat=True)
+    res = sweep.run_sweep(model, ["Dust", "Trees"], vu.get_baseline_words(4), [0.2, 0.5, 0.8], [2.0, 8.0], n_trials=4,
+                          max_new_tokens=5, temperature=0.0, batch_size=8, output_dir=os.path.join(out_dir, "sweep"))
+    mine = {(f, a) for i, f in enumerate([0.2, 0.5, 0.8]) if i % world == rank for a in (2.0, 8.0)}
+    assert set(res) == ({(f, a) for f in (0.2, 0.5, 0.8) for a in (2.0, 8.0)} if rank == 0 else mine)
+    if rank == 0:
+        torch.save(res, os.path.join(out_dir, "sweep_rank0.pt"))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -90,3 +104,18 @@ def test_world_size_2_gloo(tmp_path):
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     a, b = np.load(tmp_path / "vec0.npy"), np.load(tmp_path / "vec1.npy")
     assert np.array_equal(a, b)  # every rank ends with the same vectors
+    # the two-rank sweep gathered on rank 0 == the same sweep in one process; every configuration's files exist
+    import json
+    import sys
+
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_reference_sweep_dropin import ScriptedModel
+    from introspective_awareness_b200 import sweep, vector_utils as vu
+
+    two = torch.load(tmp_path / "sweep_rank0.pt")
+    one = sweep.run_sweep(ScriptedModel(chat=True), ["Dust", "Trees"], vu.get_baseline_words(4), [0.2, 0.5, 0.8], [2.0, 8.0],
+                          n_trials=4, max_new_tokens=5, temperature=0.0, batch_size=8, output_dir=str(tmp_path / "single"))
+    assert two == one
+    for (f, a), rows in one.items():
+        blob = json.load(open(tmp_path / "sweep" / "spy_model" / f"layer_{f:.2f}_strength_{a}" / "results.json"))
+        assert blob["results"] == rows
