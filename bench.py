@@ -70,7 +70,7 @@ def peak_hbm():
 def traffic_from_profiles(form: str):
     """dram read+write bytes per launch of the prompt-pass K2, from the committed ncu --set full summary of the
     form that was launched ("add": residual-add form, "tail": Gemma-2 block tail, "plain")."""
-    for name in {"add": ["r2_k2_add_tma_4096_ncu_summary.json", "k2_add_prefill_ncu_summary.json"],
+    for name in {"add": ["r2_k2_add_stream_4096_ncu_summary.json", "k2_add_prefill_ncu_summary.json"],
                  "tail": ["r2_k2_tail_stream_3584_ncu_summary.json"],
                  "plain": ["r2_k2_plain_tma_4096_ncu_summary.json", "k2_prefill_ncu_summary.json"]}[form]:
         try:
@@ -447,8 +447,8 @@ def run_ours(args):
     moved = (nvec * (4 if fifth else 2) + (0 if fifth else steered_vecs)) * H * 2
     traffic, traffic_src = traffic_from_profiles(form)
     # which implementation the library picks for this launch (csrc/ia_inject_rmsnorm.cu, k2_entry)
-    impl_name = ("ia::k2_stream_kernel: row in registers, quarter-row cp.async.bulk landing slots" if form != "plain" and H == 3584
-                 else "ia::k2_tma_kernel: cp.async.bulk staged rows")
+    impl_name = ("ia::k2_stream_kernel: row in registers, quarter-row cp.async.bulk landing slots"
+                 if H in (3584, 4096, 5120) and (form != "plain" or H == 5120) else "ia::k2_tma_kernel: cp.async.bulk staged rows")
 
     h2d = sum(t.numel() * t.element_size() for t in (arm.h_c_ids, arm.h_c_mask, arm.h_b_ids, arm.h_b_mask, arm.h_ids, arm.h_mask)) \
         + N_CONCEPTS * H * 2 + rows * (4 + 4 + 4)

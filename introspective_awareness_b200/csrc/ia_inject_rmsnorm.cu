@@ -318,12 +318,12 @@ static int k2_entry(K2Form form, void *h, const void *other, void *y, const void
     p.cap_out = cap_out; p.cap_tok = cap_tok; p.cap_t = cap_t;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     // Implementation choice (same bits every way), as measured on B200 at 25 600 vectors, cold, every vector
-    // steered (tools/kbench.py --r2, profiles/r2_kbench_ladder.jsonl):
-    //   * two-operand forms (Gemma-2 block tail, residual add) at H = 3584: the streaming kernel — row in
-    //     registers, quarter-row landing slots, every DRAM operand by bulk copy (tail 126 vs 156 us, add 128 vs 144);
-    //   * at H = 4096 / 5120 the streaming kernel is slower than the staged one (plain 143 vs 115 us, add 172-194
-    //     vs 166; 5120 spills registers at 10 warps), and for the plain form it is no faster at any width, so those
-    //     stay on the bulk-copy staged kernel, which also serves every short launch (lowest latency);
+    // steered (tools/kbench.py --r2, profiles/r2_kbench_ladder.jsonl; table in ia_inject_rmsnorm_stream.cu):
+    //   * long launches of the two-operand forms (residual add, Gemma-2 block tail), and of the plain form at
+    //     H = 5120: the streaming kernel — row in registers, quarter-row landing slots, every DRAM operand by
+    //     bulk copy (add form at H = 4096: 147 us against 167);
+    //   * everything else with rows of a few KiB, and every short launch: the bulk-copy staged kernel (lowest
+    //     latency; plain form 111 us at 25 600 x 4096, the streaming kernel 116);
     //   * short rows, fp32 tables, other H: the register / two-pass kernels.
     const bool stream_ok = k2_stream_supported(p, dtype, vec_dtype);
     if (flags & IA_IMPL_STREAM) {
@@ -339,7 +339,7 @@ static int k2_entry(K2Form form, void *h, const void *other, void *y, const void
         return launch_k2_tma(p, dtype, vec_dtype, variant, flags, s);
     }
     if (!(flags & IA_IMPL_REGS)) {
-        if (stream_ok && p.nvec >= kStreamMinVectors && form != kPlain && H == 3584)
+        if (stream_ok && p.nvec >= kStreamMinVectors && (form != kPlain || H == 5120))
             return launch_k2_stream(p, dtype, vec_dtype, variant, flags, s);
         if (tma_ok && (form != kPlain || row_bytes >= 4096)) return launch_k2_tma(p, dtype, vec_dtype, variant, flags, s);
     }

@@ -18,10 +18,13 @@
 //
 // Covers 16-bit model dtypes with the table in the model dtype and H in {3584, 4096, 5120} (Gemma-2-9B,
 // Llama-3.1-8B, Qwen2.5-32B: the BASELINE.json architectures) plus {1024, 2048} for tests; forced with
-// IA_IMPL_STREAM.  Chosen automatically only where it measured faster than the staged kernel on B200: the
-// two-operand forms at H = 3584 in launches of >= 8192 vectors (Gemma-2 block tail 126 vs 156 us, residual add
-// 128 vs 144 us at 25 600 vectors; 0.89 of the copy bandwidth on the bytes DRAM must move).  At H = 4096 it is
-// slower than the staged kernel (row pitch a power of two: plain 143 vs 115 us) and at 5120 it spills.
+// IA_IMPL_STREAM.  Chosen automatically for launches of >= 8192 vectors where it measured faster than the
+// staged kernel on B200 (25 600 vectors, cold L2, every vector steered; staged kernel in brackets):
+//   residual-add form   H = 4096: 147 us (167)   H = 5120: 181 us (213)   H = 3584: 129 us (144)
+//   Gemma-2 block tail  H = 3584: 127 us (158)
+//   plain form          H = 5120: 139 us (150); at 4096 / 3584 the two are level (116 / 111, 101 / 99): staged kept
+// i.e. 0.87-0.89 of the measured copy bandwidth on the bytes DRAM must move for the two-operand forms (0.94 at
+// 262 144 vectors), where a torch copy of the same byte count reaches 0.96.
 
 #include <atomic>
 
@@ -42,8 +45,8 @@ template <typename T> __device__ __forceinline__ void sumsq4_fma(const Pack4<T> 
     a3 = __fmaf_rn(f[3], f[3], a3);
 }
 
-// A row is cut into kChunks pieces ("quarter rows": 4, or 5 at H = 5120); GPC = 4-element groups per lane per
-// piece (H = 128 * kChunks * GPC); NS = landing slots per warp.
+// A row is cut into kChunks pieces ("quarter rows" in the comments; 4, 5 or 8 of them); GPC = 4-element groups per
+// lane per piece (H = 128 * kChunks * GPC); NS = landing slots per warp.
 template <typename T, int VARIANT, bool IEEE, int FORM, int kChunks, int GPC, int NS, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) k2_stream_kernel(const K2Params p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -271,9 +274,12 @@ template <typename T> static int stream_h(const K2Params &p, int variant, int fl
     switch (p.H) {
     case 1024: return stream_form<T, 4, 2, 512>(p, variant, flags, s);
     case 2048: return stream_form<T, 4, 4, 512>(p, variant, flags, s);
+    // pieces per row x groups per lane per piece x threads per CTA, as measured on B200 (25 600 vectors, cold):
+    // 1 KiB pieces at H = 4096 (2 KiB pieces: residual-add form 181 us against 147); H = 5120 keeps 80 registers of
+    // row per lane, so 8 warps (no spills: 181 us against 234 with 10 warps and spills)
     case 3584: return stream_form<T, 4, 7, 384>(p, variant, flags, s);
-    case 4096: return stream_form<T, 4, 8, 384>(p, variant, flags, s);
-    case 5120: return stream_form<T, 5, 8, 320>(p, variant, flags, s);
+    case 4096: return stream_form<T, 8, 4, 384>(p, variant, flags, s);
+    case 5120: return stream_form<T, 5, 8, 256>(p, variant, flags, s);
     default: return IA_ERR_SHAPE;
     }
 }

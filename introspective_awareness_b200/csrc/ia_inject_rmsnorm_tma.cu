@@ -101,6 +101,32 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
         }
         const RowMeta cur = meta[0];
         const int stage = it % S;
+        // Operands that are not staged — the table row (L2) in the long-launch layouts, the branch row
+        // (kAddLoaded) or the residual row (kTail) from HBM — come through registers in batches of 8 groups per
+        // lane, software-pipelined: batch 0 is requested here, BEFORE the wait on the staged row (nothing in it
+        // depends on that row), and batch b+1 while batch b is being worked on (two register buffers).
+        const bool via_regs = !(ADD != kTail && STAGE_V && cur.steer) && (cur.steer || ADD != kAddNone);
+        const T *vp = vtab + (size_t)(cur.steer ? cur.vi : 0) * H;
+        const T *ap = (ADD == kTail ? hbase : abase) + (size_t)vec * H;
+        Pack4<T> vvA[8], aaA[8], vvB[8], aaB[8];
+        auto load_batch = [&](int g0, Pack4<T>(&vv)[8], Pack4<T>(&aa)[8]) {
+            if (ADD == kAddLoaded) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (g0 + 32 * u < G) aa[u] = ld4_ro<T>(ap + 4 * (g0 + 32 * u));
+            }
+            if (ADD == kTail) {  // the residual row is rewritten below: ordinary loads, not the read-only path
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (g0 + 32 * u < G) aa[u] = ld4<T>(ap + 4 * (g0 + 32 * u));
+            }
+            if (cur.steer) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (g0 + 32 * u < G) vv[u] = ld4_ro<T>(vp + 4 * (g0 + 32 * u));
+            }
+        };
+        if (via_regs) load_batch(lane, vvA, aaA);
         mbar_wait(&bars[stage], (unsigned)(it / S) & 1u);
         T *h_s = reinterpret_cast<T *>(my_stage + (size_t)stage * kRowsPerStage * row_bytes);
         const T *a_s = reinterpret_cast<const T *>(reinterpret_cast<unsigned char *>(h_s) + row_bytes);  // kAddStaged only
@@ -128,29 +154,8 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
                 st4<T>(h_s + 4 * g, x);  // and kept for the second pass
                 sumsq4<T>(x, a0, a1, a2, a3);
             }
-        } else if (cur.steer || ADD != kAddNone) {
-            // operands that are not staged (table row from L2, branch row from HBM when ADD == kAddLoaded) come
-            // through registers, 8 loads each in flight per lane (the stores below would otherwise keep the
-            // compiler from hoisting them)
-            const T *vp = vtab + (size_t)(cur.steer ? cur.vi : 0) * H;
-            const T *ap = (ADD == kTail ? hbase : abase) + (size_t)vec * H;
-            for (int g0 = lane; g0 < G; g0 += 32 * 8) {
-                Pack4<T> vv[8], aa[8];
-                if (ADD == kAddLoaded) {
-#pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (g0 + 32 * u < G) aa[u] = ld4_ro<T>(ap + 4 * (g0 + 32 * u));
-                }
-                if (ADD == kTail) {  // the residual row is rewritten below: ordinary loads, not the read-only path
-#pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (g0 + 32 * u < G) aa[u] = ld4<T>(ap + 4 * (g0 + 32 * u));
-                }
-                if (cur.steer) {
-#pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (g0 + 32 * u < G) vv[u] = ld4_ro<T>(vp + 4 * (g0 + 32 * u));
-                }
+        } else if (via_regs) {
+            auto work_batch = [&](int g0, const Pack4<T>(&vv)[8], const Pack4<T>(&aa)[8]) {
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const int g = g0 + 32 * u;
@@ -169,6 +174,22 @@ __global__ void __launch_bounds__(512, 1) k2_tma_kernel(const K2Params p) {
                         st4<T>(h_s + 4 * g, x);
                         sumsq4<T>(x, a0, a1, a2, a3);
                     }
+                }
+            };
+            constexpr int kBatch = 32 * 8;
+            if (sizeof(T) == 2) {
+                for (int g0 = lane; g0 < G; g0 += 2 * kBatch) {
+                    if (g0 + kBatch < G) load_batch(g0 + kBatch, vvB, aaB);
+                    work_batch(g0, vvA, aaA);
+                    if (g0 + kBatch < G) {
+                        if (g0 + 2 * kBatch < G) load_batch(g0 + 2 * kBatch, vvA, aaA);
+                        work_batch(g0 + kBatch, vvB, aaB);
+                    }
+                }
+            } else {  // 4-byte elements: a second register buffer would spill; one batch at a time
+                for (int g0 = lane; g0 < G; g0 += kBatch) {
+                    if (g0 != lane) load_batch(g0, vvA, aaA);
+                    work_batch(g0, vvA, aaA);
                 }
             }
         } else {
