@@ -53,7 +53,7 @@ extern "C" {
 #define IA_IMPL_REGS 8   /* force the register-resident implementation */
 #define IA_IMPL_ADD_STAGED 16 /* ia_add_inject_rmsnorm: bulk-copy the branch row into the stage even in long launches */
 #define IA_IMPL_STREAM 32 /* force the streaming implementation (row in registers, quarter-row bulk-copy landing slots) */
-/* no IMPL bit: automatic, by measurement — streaming for launches of >= 8192 vectors of the two-operand forms
+/* no IMPL bit: automatic, by measurement — streaming for launches of >= 3000 vectors of the two-operand forms
  * (residual add, Gemma-2 block tail; plain form too at H = 5120) where it applies (16-bit dtypes, table in the model
  * dtype, H in 1024/2048/3584/4096/5120); TMA staging otherwise when a row is >= 4 KiB (always for the two-operand
  * forms) and the table is in the model dtype; else registers. */

@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(128) k2_twopass_kernel(const K2Params p) {
     }
 }
 
-constexpr int kStreamMinVectors = 8192;  // below this a launch is latency-bound: the staged kernel's layout wins
+constexpr int kStreamMinVectors = 3000;  // measured level or ahead from 3000 vectors on; shorter launches are latency-bound: staged kernel
 
 int sm_count() {
     static int cached[64] = {0};

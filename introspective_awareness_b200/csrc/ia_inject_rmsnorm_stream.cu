@@ -18,7 +18,7 @@
 //
 // Covers 16-bit model dtypes with the table in the model dtype and H in {3584, 4096, 5120} (Gemma-2-9B,
 // Llama-3.1-8B, Qwen2.5-32B: the BASELINE.json architectures) plus {1024, 2048} for tests; forced with
-// IA_IMPL_STREAM.  Chosen automatically for launches of >= 8192 vectors where it measured faster than the
+// IA_IMPL_STREAM.  Chosen automatically for launches of >= 3000 vectors where it measured faster than the
 // staged kernel on B200 (25 600 vectors, cold L2, every vector steered; staged kernel in brackets):
 //   residual-add form   H = 4096: 147 us (167)   H = 5120: 181 us (213)   H = 3584: 129 us (144)
 //   Gemma-2 block tail  H = 3584: 127 us (158)
