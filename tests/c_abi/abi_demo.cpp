@@ -130,6 +130,38 @@ int main(int argc, char **argv) {
     CK(cudaStreamSynchronize(st));
     CK(cudaMemcpy(got_v, dout, (size_t)L * C * HK * 4, cudaMemcpyDeviceToHost));
     if (memcmp(got_v, want_v, (size_t)L * C * HK * 4)) { printf("K1 static mismatch\n"); return 1; }
-    printf("abi_demo ok: K2 and K1 bit-exact against the scalar C restatement, called without Python or torch\n");
+
+    // ---------------- capture tap -> compact K1: what a host that drives the layer loop itself does ----------------
+    // The concept and baseline "forwards" each end in a K2 launch (residual add folded in) whose tap writes the updated
+    // last-position rows compactly; ia_meandiff_compact turns the two [L, n, H] buffers into vectors.  No pointer table.
+    typedef int (*addtap_fn)(void *, const void *, void *, const void *, const int32_t *, const float *, const int32_t *, const void *,
+                             float, int64_t, int64_t, int64_t, int32_t, int32_t, int32_t, int32_t, int32_t, void *, const int32_t *,
+                             int32_t, void *);
+    typedef int (*compact_fn)(const void *, int64_t, const void *, int64_t, int64_t, int64_t, int32_t, int32_t, float *, void *, float *,
+                              void *, int64_t, int32_t, void *);
+    addtap_fn addtap = (addtap_fn)dlsym(lib, "ia_add_inject_rmsnorm_tap");
+    compact_fn compact = (compact_fn)dlsym(lib, "ia_meandiff_compact");
+    if (!addtap || !compact) { printf("missing tap / compact symbols\n"); return 2; }
+    float *dcap_c, *dcap_b, *dbranch, *dyk, *dwk;
+    CK(cudaMalloc(&dcap_c, (size_t)L * C * HK * 4)); CK(cudaMalloc(&dcap_b, (size_t)L * NB * HK * 4));
+    CK(cudaMalloc(&dbranch, (size_t)NB * TK * HK * 4)); CK(cudaMalloc(&dyk, (size_t)NB * TK * HK * 4)); CK(cudaMalloc(&dwk, HK * 4));
+    CK(cudaMemset(dbranch, 0, (size_t)NB * TK * HK * 4));  // a zero branch output: h + 0 = h, so the tapped rows are the rows above
+    CK(cudaMemcpy(dwk, w, HK * 4, cudaMemcpyHostToDevice));
+    for (int l = 0; l < L; ++l) {
+        rc = addtap(dconc[l], dbranch, dyk, NULL, NULL, NULL, NULL, dwk, eps, C, TK, HK, 0, IA_F32, IA_F32, IA_NORM_LLAMA, 0,
+                    dcap_c + (size_t)l * C * HK, NULL, -1, st);
+        if (rc) { printf("ia_add_inject_rmsnorm_tap rc=%d\n", rc); return 1; }
+        rc = addtap(dbase[l], dbranch, dyk, NULL, NULL, NULL, NULL, dwk, eps, NB, TK, HK, 0, IA_F32, IA_F32, IA_NORM_LLAMA, 0,
+                    dcap_b + (size_t)l * NB * HK, NULL, -1, st);
+        if (rc) { printf("ia_add_inject_rmsnorm_tap rc=%d\n", rc); return 1; }
+    }
+    CK(cudaMemset(dout, 0, (size_t)L * C * HK * 4));
+    rc = compact(dcap_c, C, dcap_b, NB, L, HK, IA_MODE_BASELINE, 0, NULL, dout, NULL, dws, need, IA_F32, st);
+    if (rc) { printf("ia_meandiff_compact rc=%d\n", rc); return 1; }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaMemcpy(got_v, dout, (size_t)L * C * HK * 4, cudaMemcpyDeviceToHost));
+    if (memcmp(got_v, want_v, (size_t)L * C * HK * 4)) { printf("tap -> compact K1 mismatch\n"); return 1; }
+    printf("abi_demo ok: K2, its capture tap and K1 (gathered, static-scratch, compact) bit-exact against the scalar C restatement, "
+           "called without Python or torch\n");
     return 0;
 }
