@@ -133,3 +133,46 @@ def test_silu_mul_is_bit_identical_to_the_two_eager_kernels(dtype, rows, width, 
     got3 = kernels.silu_mul(gate.reshape(1, rows, width) if not fused else gate.unflatten(0, (1, rows)),
                             up.reshape(1, rows, width) if not fused else up.unflatten(0, (1, rows)))
     assert torch.equal(got3[0], want)
+
+
+@pytest.mark.parametrize("arch", ["tiny-llama", "tiny-gemma2"])
+def test_one_set_of_decode_graphs_serves_every_layer_and_sessions_are_kept(arch):
+    """The steered layer is data in the decode graphs (one row of vector indices per decoder layer, -1 except at
+    the steered one), so a sweep over layers re-uses the graphs of its batch shape; the last few batch shapes
+    keep their sessions.  Every layer's tokens and logits must still be the hook path's."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from introspective_awareness_b200.model_utils import ModelWrapper
+    from introspective_awareness_b200.synthetic import synthetic_prompt_ids
+    from oracle import ref_hooks
+
+    w = ModelWrapper.from_arch(arch, device="cuda:0", dtype=torch.bfloat16, seed=23)
+    V = w.model.config.vocab_size
+    rows = 12
+    ids, mask, lens = synthetic_prompt_ids(rows, 30, 20, V, seed=4)
+    table = (torch.randn(4, w.engine.hidden, generator=torch.Generator().manual_seed(2)) * 0.5).to(torch.bfloat16)
+    t0 = (lens - 9).tolist()
+    row_vec = [i % 5 - 1 for i in range(rows)]  # includes control rows
+    graphs_seen = None
+    for layer in (0, 1, 2, 3, 1):
+        ours = w.steered_generate_ids(ids, mask, layer, table, row_vec, [4.0] * rows, t0, 10, keep_logits=True).cpu().clone()
+        logits = torch.stack(w.last_session.step_logits).cpu()
+        sess = w.last_session
+        assert len(w.engine._sessions) == 1 and len(sess.graphs) == 1            # one shape, one set of step graphs
+        these = [id(g) for g in next(iter(sess.graphs.values()))]
+        assert graphs_seen is None or these == graphs_seen, "graphs were captured again for another layer"
+        graphs_seen = these
+        vec_rows = [table[j] if j >= 0 else torch.zeros_like(table[0]) for j in row_vec]  # a zero vector = a control row
+        ref = ref_hooks.steered_generate(w.model, ids, mask, layer, vec_rows, 4.0, t0, 10, want_logits=True)
+        assert torch.equal(ours, ref["new_ids"]), layer
+        assert (logits - ref["logits"]).abs().max().item() <= 2e-2, layer
+    # other shapes get their own sessions; the least recently used one goes when max_sessions is exceeded
+    first = w.last_session
+    for width in (29, 28):
+        w.steered_generate_ids(ids[:, -width:], mask[:, -width:], 1, table, row_vec, [4.0] * rows,
+                               [max(0, t - (30 - width)) for t in t0], 10)
+    assert len(w.engine._sessions) == 3 and first in w.engine._sessions.values()
+    w.steered_generate_ids(ids, mask, 1, table, row_vec, [4.0] * rows, t0, 10)              # touch the first shape
+    w.steered_generate_ids(ids[:, -27:], mask[:, -27:], 1, table, row_vec, [4.0] * rows, [max(0, t - 3) for t in t0], 10)
+    assert len(w.engine._sessions) == 3 and first in w.engine._sessions.values()          # the width-29 session went
+    assert [k[1] for k in w.engine._sessions] == [28, 30, 27]
