@@ -288,17 +288,25 @@ def gpu_hook_baseline(arm: Arm, reps: int = 2) -> dict:
     and `.cpu()` (model_utils.py:293-345), CPU vector arithmetic (vector_utils.py:541-548), then hook-steered HF
     `generate` — one call per strength because `strength` is a scalar there (model_utils.py:692, :737), i.e. four
     calls of 50 rows for the 200-row step."""
-    from oracle import ref_hooks
+    from oracle import real_ref, ref_hooks
 
     wl, model, layer = arm.wl, arm.model, arm.my_layer
+    kind = reference_kind()
 
     def step():
-        cacts = ref_hooks.capture(model, wl["c_ids"], wl["c_mask"], layer)
-        bacts = ref_hooks.capture(model, wl["b_ids"], wl["b_mask"], layer)
-        vecs = ref_hooks.concept_vectors(cacts, bacts, "baseline")
+        if kind == "reference":  # the reference's own ModelWrapper and vector_utils, on this GPU
+            w = _real_wrapper(model)
+            vecs = real_ref.concept_vectors(w, wl["c_ids"], wl["c_mask"], wl["b_ids"], wl["b_mask"], layer)
+        else:
+            cacts = ref_hooks.capture(model, wl["c_ids"], wl["c_mask"], layer)
+            bacts = ref_hooks.capture(model, wl["b_ids"], wl["b_mask"], layer)
+            vecs = ref_hooks.concept_vectors(cacts, bacts, "baseline")
         for k, a in enumerate(STRENGTHS):
             sel = list(range(k * N_CONCEPTS, (k + 1) * N_CONCEPTS))
             ids, mask = wl["ids"][sel], wl["mask"][sel]
+            if kind == "reference":
+                real_ref.steered_generate(w, ids, mask, layer, [vecs[i % N_CONCEPTS] for i in sel], a, [wl["t0"][i] for i in sel], N_NEW)
+                continue
             keep = int(mask.sum(1).max())  # each call is padded to its own width, as the tokenizer would
             ref_hooks.steered_generate(model, ids[:, -keep:], mask[:, -keep:], layer, [vecs[i % N_CONCEPTS] for i in sel], a,
                                        [wl["t0"][i] for i in sel], N_NEW)
@@ -310,10 +318,12 @@ def gpu_hook_baseline(arm: Arm, reps: int = 2) -> dict:
         step()
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t) / reps
-    return {"value": arm.rows / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "calls_per_step": len(STRENGTHS), "steps_timed": reps,
-            "what": "oracle/ref_hooks.py on the same GPU and model: torch-eager forward hooks + HF generate (DynamicCache, "
-                    "no CUDA graphs, stock attention), extraction by full-depth hooked forwards + CPU arithmetic; same 200 "
-                    "rows, 32 greedy tokens, 50 + 100 extraction prompts"}
+    return {"value": arm.rows / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "calls_per_step": len(STRENGTHS), "steps_timed": reps, "kind": kind,
+            "what": ("the reference's own ModelWrapper.generate_batch_with_multi_steering and vector_utils.extract_concept_vectors_batch "
+                     "(oracle/_ref)" if kind == "reference" else "oracle/ref_hooks.py (restated reference)")
+                    + " on the same GPU and model: torch-eager forward hooks + HF generate (DynamicCache, no CUDA graphs, stock "
+                      "attention), extraction by full-depth hooked forwards + CPU arithmetic; same 200 rows, 32 greedy tokens, "
+                      "50 + 100 extraction prompts"}
 
 
 def cold_shape(arm: Arm) -> dict:
@@ -587,16 +597,42 @@ SAME_CONFIG_NOTE = (
     "GPU-vs-CPU-sample figure. The like-for-like 'before' is gpu_hook_baseline: the reference's hook path on the same GPU.")
 
 
+_REF_WRAPPERS = {}
+
+
+def reference_kind() -> str:
+    """"reference": oracle/_ref holds the real reference (compiled by oracle/build_ref.py) and the legs below run ITS
+    ModelWrapper / vector_utils; "port": they run the restatement in oracle/ref_hooks.py."""
+    from oracle import real_ref
+
+    return "reference" if real_ref.load() is not None else "port"
+
+
+def _real_wrapper(model):
+    from oracle import real_ref
+
+    w = _REF_WRAPPERS.get(id(model))
+    if w is None:
+        p = next(model.parameters())
+        w = _REF_WRAPPERS[id(model)] = real_ref.wrap(model, str(p.device), p.dtype)
+    return w
+
+
 def _reference_step(model, layer, wl, rows):
     """The reference's own procedure: capture + mean-diff for the full 50 concept and 100 baseline prompts
     (vector_utils.py:524-545; two full-depth hooked forwards), then hook-steered HF generate for a sample of
-    `rows` trials (model_utils.py:687-879)."""
-    from oracle import ref_hooks
+    `rows` trials (model_utils.py:687-879) — through the real reference's own functions when oracle/_ref is there."""
+    from oracle import real_ref, ref_hooks
 
+    sel = list(range(rows))
+    if real_ref.load() is not None:
+        w = _real_wrapper(model)
+        vecs = real_ref.concept_vectors(w, wl["c_ids"], wl["c_mask"], wl["b_ids"], wl["b_mask"], layer)
+        return real_ref.steered_generate(w, wl["ids"][sel], wl["mask"][sel], layer, [vecs[wl["row_vec"][i]] for i in sel],
+                                         STRENGTHS[0], [wl["t0"][i] for i in sel], N_NEW)
     cacts = ref_hooks.capture(model, wl["c_ids"], wl["c_mask"], layer)
     bacts = ref_hooks.capture(model, wl["b_ids"], wl["b_mask"], layer)
     vecs = ref_hooks.concept_vectors(cacts, bacts, "baseline")
-    sel = list(range(rows))
     ids, mask = wl["ids"][sel], wl["mask"][sel]
     keep = int(mask.sum(1).max())  # re-pad the sample to its own width, as the tokenizer would
     ids, mask = ids[:, -keep:], mask[:, -keep:]
@@ -606,9 +642,11 @@ def _reference_step(model, layer, wl, rows):
 
 
 def _sample_text(rows, arch):
+    how = ("the reference's own vector_utils.extract_concept_vectors_batch and ModelWrapper.generate_batch_with_multi_steering "
+           "(oracle/_ref, compiled from the reference by oracle/build_ref.py; prompts = the synthetic ids written out as numbers)"
+           if reference_kind() == "reference" else "reference procedure restated in oracle/ref_hooks.py (HF generate + forward hook)")
     return (f"{rows} steered trials per step (prompt <= {T_PROMPT}, {N_NEW} greedy tokens) + extraction of the full {N_CONCEPTS} concept / "
-            f"{N_BASE} baseline prompts; reference procedure restated in oracle/ref_hooks.py (HF generate + forward hook), "
-            f"{arch} arch bf16 on the host CPU")
+            f"{N_BASE} baseline prompts; {how}, {arch} arch bf16 on the host CPU")
 
 
 def _use_all_host_threads() -> int:
@@ -631,11 +669,11 @@ def cpu_baseline_port(gpu_model, layer, wl, sample_rows=8):
         dt = time.perf_counter() - t
         arch = getattr(gpu_model.config, "model_type", "?")
         del model
-        return {"value": sample_rows / dt, "unit": UNIT, "cores": threads, "kind": "port", "seconds": dt,
+        return {"value": sample_rows / dt, "unit": UNIT, "cores": threads, "kind": reference_kind(), "seconds": dt,
                 "host_cpus": os.cpu_count(), "sample": _sample_text(sample_rows, arch) + ", one cold pass",
                 "same_config_note": SAME_CONFIG_NOTE.format(rows=sample_rows)}
     except Exception as exc:  # report, do not kill the GPU measurement
-        return {"value": None, "unit": UNIT, "cores": threads, "kind": "port", "sample": f"failed: {exc!r}"}
+        return {"value": None, "unit": UNIT, "cores": threads, "kind": reference_kind(), "sample": f"failed: {exc!r}"}
 
 
 def run_reference(args):
@@ -664,7 +702,7 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random-init weights, stub-tokenised uniform ids)",
         "config": {"workload": f"BASELINE configs[1] on the CPU, bounded sample: {sample}", "layers": [layer],
                    "same_config_note": SAME_CONFIG_NOTE.format(rows=rows)},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": reference_kind(), "sample": sample,
                          "host_cpus": os.cpu_count()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

@@ -1,0 +1,97 @@
+"""ORACLE — test infrastructure.  The REAL reference (`oracle/_ref/`, built by `oracle/build_ref.py`) on token ids.
+
+`bench.py` works on synthetic token ids; the reference's API takes strings and tokenizes them itself.  `IdTokenizer`
+closes that gap without touching the reference: a prompt is the ids written out as decimal numbers, and the tokenizer
+reads them back (left padding, pad id 0, the mapping-with-`.to()` the reference expects; no chat template, so the
+reference's helpers take their plain-text fallback and whatever words that adds are ignored).  `wrap()` builds the
+reference's own `ModelWrapper` around an existing HF model the way `oracle/make_golden.py` does (its `__init__` needs the
+Hub).  Everything that then runs — hooks, `model.generate`, the vector arithmetic — is the reference's own code.
+
+Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s baseline legs may import this.
+"""
+
+from __future__ import annotations
+
+import importlib
+import os
+import re
+import sys
+from typing import List, Optional, Sequence
+
+import torch
+
+from introspective_awareness_b200.stub_tokenizer import StubTokenizer
+
+REF_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+_INT = re.compile(r"\d+")
+_modules = None
+
+
+def load():
+    """(model_utils, vector_utils) of the real reference, or None when oracle/_ref is missing or unusable."""
+    global _modules
+    if _modules is not None:
+        return _modules or None
+    _modules = False
+    if not os.path.exists(os.path.join(REF_DIR, "model_utils.pyc")):
+        return None
+    saved = {k: sys.modules.get(k) for k in ("model_utils", "vector_utils")}
+    sys.path.insert(0, REF_DIR)
+    try:
+        for k in saved:
+            sys.modules.pop(k, None)
+        mu = importlib.import_module("model_utils")
+        vu = importlib.import_module("vector_utils")
+        if not str(getattr(mu, "__file__", "")).startswith(REF_DIR):
+            raise ImportError("another model_utils shadows oracle/_ref")
+        _modules = (mu, vu)
+    except Exception:
+        _modules = False
+    finally:
+        sys.path.remove(REF_DIR)
+        for k, v in saved.items():  # leave the names as we found them; the reference modules stay reachable through us
+            if v is not None:
+                sys.modules[k] = v
+            elif not _modules:
+                sys.modules.pop(k, None)
+    return _modules or None
+
+
+class IdTokenizer(StubTokenizer):
+    """Prompts are token ids written as decimal numbers; anything that is not a number is ignored."""
+
+    def encode(self, text: str) -> List[int]:
+        return [int(t) for t in _INT.findall(text)]
+
+
+def ids_to_prompts(ids: torch.Tensor, mask: torch.Tensor) -> List[str]:
+    return [" ".join(str(int(t)) for t in row[m.bool()]) for row, m in zip(ids, mask)]
+
+
+def wrap(model, device: str, dtype: torch.dtype):
+    """The reference's ModelWrapper around `model` (reference model_utils.py:56-137, minus the Hub download)."""
+    mu, _ = load()
+    w = mu.ModelWrapper.__new__(mu.ModelWrapper)
+    w.model_name, w.hf_path = "synthetic", "synthetic"
+    w.device, w.dtype = device, dtype
+    w.model = model
+    w.tokenizer = IdTokenizer(vocab_size=model.config.vocab_size)
+    w.hooks = []
+    w.n_layers = w._get_n_layers()
+    return w
+
+
+def concept_vectors(w, c_ids, c_mask, b_ids, b_mask, layer_idx: int):
+    """reference vector_utils.extract_concept_vectors_batch on id prompts -> [C, H] in the model dtype (CPU)."""
+    _, vu = load()
+    cw, bw = ids_to_prompts(c_ids, c_mask), ids_to_prompts(b_ids, b_mask)
+    vecs = vu.extract_concept_vectors_batch(w, cw, bw, layer_idx=layer_idx, extraction_method="baseline", template="{word}")
+    return torch.stack([vecs[k] for k in cw])
+
+
+def steered_generate(w, ids, mask, layer_idx: int, vectors: Sequence[torch.Tensor], strength: float,
+                     start_positions: Optional[Sequence[int]], max_new_tokens: int) -> List[str]:
+    """reference ModelWrapper.generate_batch_with_multi_steering on id prompts (greedy)."""
+    return w.generate_batch_with_multi_steering(
+        prompts=ids_to_prompts(ids, mask), layer_idx=layer_idx, steering_vectors=list(vectors), strength=strength,
+        max_new_tokens=max_new_tokens, temperature=0.0, steering_start_positions=list(start_positions))
