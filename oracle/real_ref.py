@@ -12,7 +12,6 @@ Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s baseline legs may impo
 
 from __future__ import annotations
 
-import importlib
 import os
 import re
 import sys
@@ -27,32 +26,38 @@ _INT = re.compile(r"\d+")
 _modules = None
 
 
+def _load_one(name: str):
+    """Import oracle/_ref/<name>.bin (byte code compiled from the reference's <name>.py) as module `name`."""
+    from importlib.machinery import SourcelessFileLoader
+    from importlib.util import module_from_spec, spec_from_file_location
+
+    path = os.path.join(REF_DIR, name + ".bin")
+    spec = spec_from_file_location(name, path, loader=SourcelessFileLoader(name, path))
+    mod = module_from_spec(spec)
+    sys.modules[name] = mod  # vector_utils does `from model_utils import ...`
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def load():
-    """(model_utils, vector_utils) of the real reference, or None when oracle/_ref is missing or unusable."""
+    """(model_utils, vector_utils) of the real reference, or None when oracle/_ref is missing or unusable
+    (e.g. compiled by another Python version)."""
     global _modules
     if _modules is not None:
         return _modules or None
     _modules = False
-    if not os.path.exists(os.path.join(REF_DIR, "model_utils.pyc")):
+    if not os.path.exists(os.path.join(REF_DIR, "model_utils.bin")):
         return None
     saved = {k: sys.modules.get(k) for k in ("model_utils", "vector_utils")}
-    sys.path.insert(0, REF_DIR)
     try:
-        for k in saved:
-            sys.modules.pop(k, None)
-        mu = importlib.import_module("model_utils")
-        vu = importlib.import_module("vector_utils")
-        if not str(getattr(mu, "__file__", "")).startswith(REF_DIR):
-            raise ImportError("another model_utils shadows oracle/_ref")
-        _modules = (mu, vu)
+        _modules = (_load_one("model_utils"), _load_one("vector_utils"))
     except Exception:
         _modules = False
     finally:
-        sys.path.remove(REF_DIR)
         for k, v in saved.items():  # leave the names as we found them; the reference modules stay reachable through us
             if v is not None:
                 sys.modules[k] = v
-            elif not _modules:
+            else:
                 sys.modules.pop(k, None)
     return _modules or None
 

@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _real_ref():
     from oracle import build_ref, real_ref
 
-    if not os.path.exists(os.path.join(real_ref.REF_DIR, "model_utils.pyc")):
+    if not os.path.exists(os.path.join(real_ref.REF_DIR, "model_utils.bin")):
         build_ref.build(verbose=False)  # the build container has /root/reference; the GPU box gets the built files
     if real_ref.load() is None:
         pytest.skip("oracle/_ref not built (no /root/reference here)")
