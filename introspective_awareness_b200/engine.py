@@ -157,11 +157,17 @@ class StaticKV:
     `pos` is a host integer, so the returned views have exact length — the same shapes a
     DynamicCache would hand to SDPA — and are static inside a per-step CUDA graph."""
 
-    def __init__(self, n_layers: int, batch: int, n_kv: int, max_len: int, head_dim: int, dtype, device):
+    def __init__(self, n_layers: int, batch: int, n_kv: int, max_len: int, head_dim: int, dtype, device,
+                 sliding_layers: Sequence[int] = (), sliding_window: Optional[int] = None):
         self.k = [torch.empty(batch, n_kv, max_len, head_dim, dtype=dtype, device=device) for _ in range(n_layers)]
         self.v = [torch.empty(batch, n_kv, max_len, head_dim, dtype=dtype, device=device) for _ in range(n_layers)]
         self.pos = 0
         self.max_len = max_len
+        # Gemma-2's sliding-attention layers: on a cached step HF's sliding cache hands attention the last
+        # `sliding_window` keys only (the new one included), not the whole history under a mask — same maths, but
+        # the attention kernel then sums over another number of keys, i.e. in another order.  Same views here.
+        self.sliding_layers = frozenset(sliding_layers)
+        self.sliding_window = sliding_window
 
     def update(self, key_states, value_states, layer_idx, *args, **kwargs):
         t = key_states.shape[2]
@@ -170,7 +176,14 @@ class StaticKV:
             raise RuntimeError("StaticKV overflow")
         self.k[layer_idx][:, :, self.pos:end].copy_(key_states)
         self.v[layer_idx][:, :, self.pos:end].copy_(value_states)
-        return self.k[layer_idx][:, :, :end], self.v[layer_idx][:, :, :end]
+        lo = self.window_start(layer_idx, t, end)
+        return self.k[layer_idx][:, :, lo:end], self.v[layer_idx][:, :, lo:end]
+
+    def window_start(self, layer_idx: int, t: int, end: int) -> int:
+        """First key a cached step (t == 1) of a sliding-attention layer sees; 0 everywhere else."""
+        if t == 1 and self.sliding_window is not None and layer_idx in self.sliding_layers and end > self.sliding_window:
+            return end - self.sliding_window
+        return 0
 
     def bytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in self.k + self.v)
@@ -762,7 +775,9 @@ class Session:
         b, t, n, padded, n_vec_cap, vec_dtype = key
         dev = eng.device
         self.B, self.T, self.N, self.padded = b, t, n, padded
-        self.cache = StaticKV(eng.n_layers, b, eng.n_kv, t + max(n - 1, 0), eng.head_dim, eng.dtype, dev)
+        sliding = [i for i in range(eng.n_layers) if eng._layer_kind(i) == "sliding_attention"] if eng.sliding_window else []
+        self.cache = StaticKV(eng.n_layers, b, eng.n_kv, t + max(n - 1, 0), eng.head_dim, eng.dtype, dev,
+                              sliding_layers=sliding, sliding_window=eng.sliding_window)
         self.key_valid = torch.ones(b, t + n, dtype=torch.bool, device=dev)
         self.tok = torch.zeros(b, 1, dtype=torch.long, device=dev)
         self.posid = torch.zeros(b, 1, dtype=torch.long, device=dev)
@@ -815,9 +830,9 @@ class Session:
         full = self.key_valid[:, None, None, :length] if self.padded else None
         masks = {"full_attention": full, "sliding_attention": full}
         if eng.sliding_window is not None and length > eng.sliding_window:
-            k = torch.arange(length, device=h.device)
-            win = (k > length - 1 - eng.sliding_window)[None, None, None, :]
-            masks["sliding_attention"] = win.expand(self.B, 1, 1, length) if full is None else (full & win)
+            # sliding layers get the last `sliding_window` keys (StaticKV.update): every one of them is inside the
+            # window, so only the padding mask is left, cut to the same keys
+            masks["sliding_attention"] = None if full is None else full[..., length - eng.sliding_window:]
         final, _ = eng.run_layers(h, pos_emb, masks, eng_cache, steer=steer, pos0=self.T + s - 1, decode=True)
         lg = eng.logits(final)
         if self.logits_buf is not None:

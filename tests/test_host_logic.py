@@ -319,3 +319,22 @@ def test_fused_linear_shares_storage_and_keeps_module_outputs():
         assert part.shape == a0.shape and torch.allclose(part, a0, rtol=1e-5, atol=1e-6)
     assert sum(fused.sizes) == fused.W.shape[0] and set(k for k in model.state_dict() if "layers.0.self_attn" in k) >= {
         "model.layers.0.self_attn.q_proj.weight", "model.layers.0.self_attn.k_proj.bias"}
+
+
+def test_gemma2_sliding_window_steps_match_hf_generate():
+    """Cached steps past Gemma-2's sliding window: the sliding layers see the last `sliding_window` keys only, as HF's
+    sliding cache hands them over (tiny stand-in: window 64; prompts of 50-60 tokens, 24 new tokens cross it)."""
+    from introspective_awareness_b200.model_utils import ModelWrapper
+    from introspective_awareness_b200.synthetic import synthetic_prompt_ids
+
+    w = ModelWrapper.from_arch("tiny-gemma2", device="cpu", dtype=torch.float32, seed=5)
+    assert w.engine.sliding_window == 64
+    ids, mask, _ = synthetic_prompt_ids(3, 60, 50, w.model.config.vocab_size, seed=8)
+    with torch.no_grad():
+        ref = w.model.generate(input_ids=ids, attention_mask=mask, max_new_tokens=24, do_sample=False, pad_token_id=0,
+                               output_logits=True, return_dict_in_generate=True)
+    got = w.steered_generate_ids(ids, mask, None, None, None, None, None, 24, keep_logits=True)
+    ours = torch.stack(w.last_session.step_logits)
+    theirs = torch.stack([l.float() for l in ref.logits])
+    assert torch.equal(got, ref.sequences[:, 60:])
+    assert (ours - theirs).abs().max().item() <= 1e-4
