@@ -252,6 +252,10 @@ def test_string_api_matches_hook_path_text():
     assert one == w.tokenizer.decode(ref_hooks.steered_generate(
         w.model, enc["input_ids"][:1, enc["input_ids"].shape[1] - lens[0]:], enc["attention_mask"][:1, enc["input_ids"].shape[1] - lens[0]:],
         1, [vecs["Dust"]], 4.0, [t0[0]], 12)["new_ids"][0], skip_special_tokens=True).strip()
+    # a vector index beyond the table is refused up front (the kernels take no table length)
+    ids_, mask_ = w._encode(prompts)
+    with pytest.raises(IndexError, match="row_vec"):
+        w.steered_generate_ids(ids_, mask_, 1, torch.stack([vecs[c] for c in concepts]), [0, 1, 3], [4.0] * 3, t0, 4)
     # same-vector batch entry point works (the reference's raises UnboundLocalError)
     outs = w.generate_batch_with_steering(prompts, 1, vecs["Dust"], strength=2.0, max_new_tokens=4, temperature=0.0,
                                           steering_start_pos=t0[0])
