@@ -8,9 +8,11 @@ extract 50 concept vectors against 100 baseline prompts at the steering layer (t
 capture tap + K1), then run 200 steered trials (50 concepts x 4 strengths, one batch, a different
 (concept, alpha, t0) per row) for 32 greedy tokens each (prompt pass + 31 cached decode steps, K2 at the
 layer in each).  With N > 1 every rank is an independent replica steering its own layer of the sweep
-(configs[2], weak scaling); extraction is then prompt-sharded through the product API
-(`ModelWrapper.extract_vectors_sharded_ids`: one all-reduce of the fp32 baseline sums, one all-gather
-of the concept rows), and the token ids are gathered to rank 0.
+(configs[2], weak scaling): it extracts its own layer's vectors from the whole prompt sets (the reference's
+batch composition, so the reference's bits at any rank count) and the token ids are gathered to rank 0 over
+NCCL; `--sharded-extraction` splits the prompts over the ranks instead (`ModelWrapper.extract_vectors_sharded_ids`:
+one all-reduce of the fp32 baseline sums, one all-gather of the concept rows) — faster, but each rank's forward is
+then a smaller GEMM problem and the bf16 activations move with the rank count (`parity_check` reports by how much).
 
 Prints ONE JSON line on rank 0.  `value` times the path with inputs resident in HBM; `e2e` times the
 same work through the public ModelWrapper-level API with pinned HOST buffers (H2D of ids / masks /
@@ -146,7 +148,7 @@ def make_workload(vocab: int, rank: int):
 class Arm:
     """One architecture on this rank: model, wrapper, workload, and the two step functions."""
 
-    def __init__(self, arch, attention, rank, world, local):
+    def __init__(self, arch, attention, rank, world, local, sharded_extraction=False):
         from introspective_awareness_b200 import parallel
         from introspective_awareness_b200.engine import SteerSpec
         from introspective_awareness_b200.model_utils import ModelWrapper, get_layer_at_fraction
@@ -154,6 +156,7 @@ class Arm:
         from introspective_awareness_b200.synthetic import build_model
 
         self.arch, self.rank, self.world = arch, rank, world
+        self.sharded_extraction = bool(sharded_extraction) and world > 1
         self.parallel, self.SteerSpec = parallel, SteerSpec
         dev = self.dev = torch.device("cuda", local)
         torch.manual_seed(0)
@@ -183,19 +186,26 @@ class Arm:
     def session(self, n_new=N_NEW):
         return self.eng.session(self.rows, T_PROMPT, n_new, padded=True, n_vec_cap=64, vec_dtype=torch.bfloat16)
 
-    def extract(self, layers, host=False):
-        """-> [len(layers), 50, H] device vectors (inputs: the HBM-resident copies, or the pinned host ones)."""
+    def extract(self, layers, host=False, sharded=None):
+        """-> [len(layers), 50, H] device vectors (inputs: the HBM-resident copies, or the pinned host ones).
+        Default: every rank extracts the layers it needs from the WHOLE prompt sets — the reference's batch
+        composition, hence the reference's bits whatever the rank count.  sharded (--sharded-extraction): the prompts
+        split over the ranks through the product API (a collective call; see parity_check for what that costs in bits)."""
         ci, cm, bi, bm = ((self.h_c_ids, self.h_c_mask, self.h_b_ids, self.h_b_mask) if host
                           else (self.c_ids, self.c_mask, self.b_ids, self.b_mask))
-        if self.world == 1:
-            _, vr, _ = self.eng.extract_vectors(ci, cm, bi, bm, layers, want_f32=False, want_norm=False)
-        else:  # prompt-sharded through the product API, for every layer of this step (collective)
+        if self.sharded_extraction if sharded is None else sharded:
             _, vr, _ = self.w.extract_vectors_sharded_ids(ci, cm, bi, bm, layers)
+        else:
+            _, vr, _ = self.eng.extract_vectors(ci, cm, bi, bm, layers, want_f32=False, want_norm=False)
         return vr
+
+    def step_layers(self):
+        """Layers one step extracts for: this rank's own, or (prompt-sharded: a collective) every rank's."""
+        return sorted(set(self.sweep)) if self.sharded_extraction else [self.my_layer]
 
     def step_resident(self, n_new=N_NEW, layer=None, table=None):
         if table is None:
-            uniq = sorted(set(self.sweep))
+            uniq = self.step_layers()
             table = self.extract(uniq)[uniq.index(self.my_layer)]
         steer = self.SteerSpec(self.my_layer if layer is None else layer, table, self.row_vec_d, self.row_alpha_d, self.t0_d)
         out = self.session(n_new).generate(self.ids_d, self.mask_d, steer, temperature=0.0, eos_token_id=None, pad_token_id=0)
@@ -206,7 +216,7 @@ class Arm:
     def step_e2e(self):
         """Public API with host buffers: ids/masks from pinned host memory, vectors returned to the host
         (as the reference's extraction does), generation fed with host vectors, ids read back."""
-        uniq = sorted(set(self.sweep))
+        uniq = self.step_layers()
         vec_host = self.extract(uniq, host=True)[uniq.index(self.my_layer)].cpu()
         wl = self.wl
         out = self.w.steered_generate_ids(self.h_ids, self.h_mask, self.my_layer, vec_host, wl["row_vec"], wl["row_alpha"], wl["t0"],
@@ -248,18 +258,23 @@ class Arm:
 # ---------------------------------------------------------------------------------------------
 
 def parity_check(arm: Arm) -> dict:
-    """N > 1, before timing.  (a) the prompt-sharded vectors (K1a -> all-reduce -> all-gather -> K1b) against the
-    un-sharded extraction of the same prompts on this rank; (b) this rank's steered rows against the reference hook
-    path (oracle/ref_hooks.py) on a 16-row subset of its own batch: first-step logits and the greedy tokens."""
+    """N > 1, before timing.  (a) this rank's vectors (extracted from the whole prompt sets, as every step does by
+    default) against the hook path's capture + CPU arithmetic on the same GPU; (b) this rank's steered rows against the
+    hook path on a 16-row subset of its own batch: first-step logits and the greedy tokens; (c) for the record, what the
+    optional prompt-sharded extraction (K1a -> all-reduce -> all-gather -> K1b) does to the bits: each rank then
+    forwards a smaller batch, cuBLAS picks other tiles for the smaller M, and the bf16 activations move."""
     from oracle import ref_hooks
 
     uniq = sorted(set(arm.sweep))
-    sharded = arm.extract(uniq)                                   # collective
+    sharded = arm.extract(uniq, sharded=True)                     # collective
     _, whole, _ = arm.eng.extract_vectors(arm.c_ids, arm.c_mask, arm.b_ids, arm.b_mask, uniq, want_f32=False, want_norm=False)
     a, b = sharded.float(), whole.float()
     rel = ((a - b).norm(dim=-1) / b.norm(dim=-1)).max().item()
     differing = (sharded != whole).float().mean().item()
     table = whole[uniq.index(arm.my_layer)].clone()
+    hook_vecs = ref_hooks.concept_vectors(ref_hooks.capture(arm.model, arm.wl["c_ids"], arm.wl["c_mask"], arm.my_layer),
+                                          ref_hooks.capture(arm.model, arm.wl["b_ids"], arm.wl["b_mask"], arm.my_layer), "baseline")
+    vec_rel = ((table.float().cpu() - hook_vecs.float()).norm(dim=-1) / hook_vecs.float().norm(dim=-1)).max().item()
     wl = arm.wl
     out = arm.w.steered_generate_ids(arm.ids_d, arm.mask_d, arm.my_layer, table, wl["row_vec"], wl["row_alpha"], wl["t0"], N_NEW,
                                      temperature=0.0, keep_logits=True).clone()
@@ -271,16 +286,20 @@ def parity_check(arm: Arm) -> dict:
     same = (out[:16].cpu() == ref["new_ids"]).all(dim=1).float().mean().item()
     arm.w.last_session.logits_buf = None  # the timed steps run the graphs without the logits copy
     arm.w.last_session.graphs.clear()
-    stats = torch.tensor([rel, differing, first, 1.0 - same], device=arm.dev)
+    stats = torch.tensor([rel, differing, first, 1.0 - same, vec_rel], device=arm.dev)
     if arm.world > 1:
         torch.distributed.all_reduce(stats, op=torch.distributed.ReduceOp.MAX)
-    rel, differing, first, miss = stats.tolist()
-    return {"sharded_vs_unsharded_vectors_rel_l2_max": rel, "sharded_vs_unsharded_fraction_of_elements_differing": differing,
-            "first_step_logits_vs_hook_path_max_abs": first, "rows_with_identical_32_token_paths": 1.0 - miss,
-            "rows_checked_per_rank": 16, "ranks": arm.world,
-            "ok": bool(rel <= 1e-3 and first <= 2e-2),
-            "note": "max over ranks; vectors: K1a -> NCCL all-reduce / all-gather -> K1b against one un-sharded extraction; logits: "
-                    "200-row batch of ours against a 16-row hook-path batch of the same rows (north_star: <= 2e-2)"}
+    rel, differing, first, miss, vec_rel = stats.tolist()
+    return {"vectors_vs_hook_path_rel_l2_max": vec_rel, "first_step_logits_vs_hook_path_max_abs": first,
+            "rows_with_identical_32_token_paths": 1.0 - miss, "rows_checked_per_rank": 16, "ranks": arm.world,
+            "ok": bool(vec_rel <= 1e-3 and first <= 2e-2),
+            "extraction_in_timed_steps": "prompt-sharded" if arm.sharded_extraction else "whole prompt sets on every rank",
+            "prompt_sharded_extraction": {"vs_unsharded_vectors_rel_l2_max": rel, "fraction_of_elements_differing": differing,
+                                          "within_north_star_1e-3": bool(rel <= 1e-3)},
+            "note": "max over ranks; vectors: each rank's extraction against ref_hooks capture + CPU arithmetic on the same GPU "
+                    "(north_star: <= 1e-3); logits: 200-row batch of ours against a 16-row hook-path batch of the same rows "
+                    "(<= 2e-2); prompt_sharded_extraction: the optional sharded protocol against the un-sharded result — a "
+                    "rank-count-dependent difference, because each rank's forward is a smaller GEMM problem"}
 
 
 def gpu_hook_baseline(arm: Arm, reps: int = 2) -> dict:
@@ -360,7 +379,10 @@ def strong_scaling(arm: Arm) -> dict:
     mine = [l for l in range(n_layers) if l % arm.world == arm.rank]
 
     def sweep():
-        vecs = arm.extract(list(range(n_layers)))
+        if arm.sharded_extraction:
+            vecs = dict(enumerate(arm.extract(list(range(n_layers)))))
+        else:  # every rank: one extraction for its own layers, from the whole prompt sets
+            vecs = dict(zip(mine, arm.extract(mine)))
         for l in mine:
             arm.step_resident(layer=l, table=vecs[l])
 
@@ -372,7 +394,7 @@ def strong_scaling(arm: Arm) -> dict:
 
 
 def measure_other_arch(arch, args, rank, world, local) -> dict:
-    arm = Arm(arch, args.attention, rank, world, local)
+    arm = Arm(arch, args.attention, rank, world, local, args.sharded_extraction)
     try:
         for _ in range(3):
             arm.step_resident()
@@ -400,7 +422,7 @@ def run_ours(args):
         raise SystemExit("bench.py (our arm) needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local)
     arch = args.arch
-    arm = Arm(arch, args.attention, rank, world, local)
+    arm = Arm(arch, args.attention, rank, world, local, args.sharded_extraction)
     eng, rows = arm.eng, arm.rows
 
     parity = None
@@ -491,6 +513,7 @@ def run_ours(args):
         cpu = cpu_baseline_port(arm.model, arm.my_layer, arm.wl, sample_rows=args.cpu_rows)
 
     sweep, fused, attention, native = arm.sweep, dict(eng._fused_checked), eng.attention, eng.native_block
+    arm_sharded = arm.sharded_extraction
     if (world == 8 or args.other_archs) and arch == ARCH and not args.no_extras:
         del eng
         arm.free()
@@ -508,7 +531,9 @@ def run_ours(args):
                 "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": attention,
                 "engine_block": "native" if native else "hf",
                 "single_gemm_projections": {f"{k}{list(shape)}": ok for (k, shape), ok in sorted(fused.items())},
-                "parallelism": "independent replicas, layer axis round-robin" if world > 1 else "single replica",
+                "parallelism": ("independent replicas, layer axis round-robin; extraction "
+                                + ("prompt-sharded (NCCL all-reduce / all-gather)" if arm_sharded else "from the whole prompt sets on every rank")
+                                if world > 1 else "single replica"),
                 "l2": "inputs larger than L2: each step streams 16 GB of weights per decode step and ~1 GB of KV/activations",
             },
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -723,6 +748,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the context figures measured outside the timed regions")
     ap.add_argument("--other-archs", action="store_true", help="also run one short step each of configs[3] / [4] (default at --gpus 8)")
+    ap.add_argument("--sharded-extraction", action="store_true",
+                    help="N > 1: split the extraction prompts over the ranks (NCCL all-reduce of fp32 sums, all-gather of concept "
+                         "rows) instead of extracting from the whole prompt sets on every rank; faster, not rank-count-invariant in bits")
     ap.add_argument("--ncu-window", action="store_true", help="cudaProfilerStart at the last timed step (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":

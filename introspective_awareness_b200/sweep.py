@@ -79,23 +79,35 @@ def save_vectors(base: Path, layer_fraction: float, vectors: Dict[str, torch.Ten
 def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], layer_fractions: Sequence[float],
               strengths: Sequence[float], n_trials: int = 30, max_new_tokens: int = 100, temperature: float = 1.0,
               batch_size: int = 256, output_dir: Optional[str] = None, extraction_method: str = "baseline",
-              with_forced: bool = True, save_vector_files: bool = True) -> Dict[tuple, List[dict]]:
+              with_forced: bool = True, save_vector_files: bool = True, sharded_extraction: bool = False
+              ) -> Dict[tuple, List[dict]]:
     """Runs the whole grid and (if output_dir) writes the reference's files.  Trial split as the reference:
     n_injection = n_trials // 2, n_control = n_trials - n_injection, forced = n_injection, numbered 1..n_injection,
     then n_injection + t, then n_injection + n_control + t (detect_injected_thoughts.py:1792-1799, :1917, :1984).
 
-    In a `torch.distributed` job (one process per GPU, `parallel.init_from_env`) this is a collective call:
-    extraction is prompt-sharded (every rank forwards its slice of the concept and baseline prompts, fp32 sums
-    all-reduced, concept rows all-gathered), each rank steers the layer fractions dealt to it round-robin and
-    writes their files, and the result rows are gathered: rank 0 returns every configuration, the other ranks
-    their own."""
+    In a `torch.distributed` job (one process per GPU, `parallel.init_from_env`) this is a collective call: each
+    rank steers the layer fractions dealt to it round-robin and writes their files, and the result rows are
+    gathered — rank 0 returns every configuration, the other ranks their own.  Extraction: by default every rank
+    extracts the layers IT steers from the whole prompt sets (the reference's batch composition, hence the
+    reference's vectors whatever the rank count; rank 0 also extracts what it needs for the vector files);
+    sharded_extraction=True splits the prompts over the ranks instead (fp32 sums all-reduced, concept rows
+    all-gathered) — faster, but every rank's forward is then a smaller GEMM problem for which cuBLAS may pick other
+    tiles, so the bf16 activations, and with them the vectors, depend on the rank count (measured at 8 ranks on
+    Llama-3.1-8B dimensions: 4e-2 relative L2 against the un-sharded vectors; identical at 2 ranks)."""
     rank, world = parallel.world()
     concepts = list(concepts)
     fractions = list(layer_fractions)
     layer_of = {f: get_layer_at_fraction(model, f) for f in fractions}
     uniq_layers = sorted(set(layer_of.values()))
-    by_layer = vu.extract_concept_vectors_multi_layer(model, concepts, list(baseline_words), uniq_layers,
-                                                      extraction_method=extraction_method, sharded=world > 1)
+    mine = parallel.shard_round_robin(fractions, rank, world)
+    if sharded_extraction and world > 1:
+        need = uniq_layers
+    else:
+        keep_all = rank == 0 and output_dir is not None and save_vector_files
+        need = uniq_layers if keep_all else sorted({layer_of[f] for f in mine})
+    by_layer = vu.extract_concept_vectors_multi_layer(model, concepts, list(baseline_words), need,
+                                                      extraction_method=extraction_method,
+                                                      sharded=sharded_extraction and world > 1) if need else {}
     base = None
     if output_dir is not None:
         base = Path(output_dir) / str(model.model_name).replace("/", "_")
@@ -105,7 +117,7 @@ def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], lay
     n_inj = n_trials // 2
     n_ctl = n_trials - n_inj
     out: Dict[tuple, List[dict]] = {}
-    for f in parallel.shard_round_robin(fractions, rank, world):
+    for f in mine:
         layer = layer_of[f]
         rows = grid.layer_trials(concepts, strengths, n_inj, n_ctl, n_inj if with_forced else 0, dedupe_control=True)
         results = grid.run_layer(model, layer, by_layer[layer], rows, max_new_tokens, temperature, batch_size,

@@ -49,12 +49,15 @@ def _worker(rank, world, port, out_dir):
         gathered = [torch.empty_like(sharded) for _ in range(world)]
         torch.distributed.all_gather(gathered, sharded)
         assert all(torch.equal(g, sharded) for g in gathered), method     # every rank ends with the same vectors
-    # the sweep as a collective call
-    res = sweep.run_sweep(m, ["Dust", "Trees", "Oceans"], vu.get_baseline_words(6), [0.3, 0.8], [2.0, 8.0], n_trials=4,
-                          max_new_tokens=5, temperature=0.0, batch_size=16, output_dir=os.path.join(out_dir, "two"))
-    if rank == 0:
-        assert set(res) == {(f, a) for f in (0.3, 0.8) for a in (2.0, 8.0)}
-        torch.save(res, os.path.join(out_dir, "two.pt"))
+    # the sweep as a collective call: default (every rank extracts its own layers from the whole prompt sets: the
+    # one-process bits) and with prompt-sharded extraction
+    for tag, sharded in (("two", False), ("two_sharded", True)):
+        res = sweep.run_sweep(m, ["Dust", "Trees", "Oceans"], vu.get_baseline_words(6), [0.3, 0.8], [2.0, 8.0], n_trials=4,
+                              max_new_tokens=5, temperature=0.0, batch_size=16, output_dir=os.path.join(out_dir, tag),
+                              sharded_extraction=sharded)
+        if rank == 0:
+            assert set(res) == {(f, a) for f in (0.3, 0.8) for a in (2.0, 8.0)}
+            torch.save(res, os.path.join(out_dir, tag + ".pt"))
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 
@@ -66,16 +69,21 @@ def test_world_size_2_nccl(tmp_path):
     from introspective_awareness_b200 import sweep, vector_utils as vu
     from introspective_awareness_b200.model_utils import ModelWrapper
 
-    two = torch.load(tmp_path / "two.pt")
+    two, two_sharded = torch.load(tmp_path / "two.pt"), torch.load(tmp_path / "two_sharded.pt")
     m = ModelWrapper.from_arch("tiny-llama", device="cuda:0", dtype=torch.bfloat16, seed=13)
     m.model_name = "tiny/llama"
     one = sweep.run_sweep(m, ["Dust", "Trees", "Oceans"], vu.get_baseline_words(6), [0.3, 0.8], [2.0, 8.0], n_trials=4,
                           max_new_tokens=5, temperature=0.0, batch_size=16, output_dir=str(tmp_path / "one"))
-    assert set(two) == set(one)
-    same = sum(a["response"] == b["response"] for k in one for a, b in zip(one[k], two[k]))
+    assert two == one  # default extraction: every rank works from the whole prompt sets, so the one-process results exactly
+    for k in sorted(one):
+        assert torch.equal(torch.load(tmp_path / "two" / "tiny_llama" / "vectors" / f"layer_{k[0]:.2f}" / "Trees.pt"),
+                           torch.load(tmp_path / "one" / "tiny_llama" / "vectors" / f"layer_{k[0]:.2f}" / "Trees.pt"))
+    # prompt-sharded extraction: the vectors may differ in the last bits (each rank's forward is a smaller GEMM problem;
+    # fp32 summation order of the sharded mean), which can move a greedy token on a random-init model: everything else —
+    # rows, order, numbering — is the same
+    assert set(two_sharded) == set(one)
+    same = sum(a["response"] == b["response"] for k in one for a, b in zip(one[k], two_sharded[k]))
     total = sum(len(v) for v in one.values())
-    # the vectors may differ in the last bit of a few elements (fp32 summation order of the sharded mean), which can
-    # move a greedy token on a random-init model: everything else — rows, order, numbering — is the same
     assert [[(r["concept"], r["trial"], r["trial_type"], r["strength"]) for r in one[k]] for k in sorted(one)] == \
-           [[(r["concept"], r["trial"], r["trial_type"], r["strength"]) for r in two[k]] for k in sorted(two)]
+           [[(r["concept"], r["trial"], r["trial_type"], r["strength"]) for r in two_sharded[k]] for k in sorted(two_sharded)]
     assert same >= 0.9 * total, (same, total)
