@@ -2,9 +2,11 @@
 # Round-2 measurement pass on one B200 (run under gpurun from the repo root): GPU tests, kernel ladder,
 # ncu --set full captures of the kernels the bench launches (exported to CSV: the reports themselves are
 # too large to bring back), the bench's launch list, and the bench lines of the three architectures.
+# SKIP_KERNELS=1 leaves out the kernel ladder, the ncu captures and the launch list (tests and bench lines only).
 mkdir -p gpurun_out
 O=gpurun_out
 timeout 1500 python -m pytest tests -m gpu -q --maxfail=10 > $O/gpu_tests.log 2>&1; echo "gpu tests rc=$?" | tee -a $O/gpu_tests.log
+if [ -z "$SKIP_KERNELS" ]; then
 timeout 900 python tools/kbench.py --r2 --reps 10 > $O/r2_kbench_ladder.jsonl 2> $O/kbench.err; echo "kbench rc=$?"
 P="python tools/kbench.py --only-rows 25600 --reps 2"
 for spec in "4096 add auto" "3584 tail auto" "4096 plain auto" "5120 add auto" "4096 add tma"; do
@@ -18,6 +20,7 @@ B="python bench.py --steps 2 --warmup 3 --no-extras --no-cpu-baseline --ncu-wind
 $B > $O/bench_window_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 3000 --csv --log-file $O/r2_bench_launches_window.csv $B > $O/bench_window_ncu.log 2>&1
 echo "launch list rc=$?"
+fi
 timeout 900 python bench.py > $O/r2_bench_n1.json 2> $O/bench_n1.err; echo "bench n1 rc=$?"
 timeout 900 python bench.py --arch gemma-2-9b --no-extras --no-cpu-baseline > $O/r2_bench_gemma2_9b.json 2> $O/bench_gemma.err; echo "bench gemma rc=$?"
 timeout 900 python bench.py --arch qwen2.5-32b --no-extras --no-cpu-baseline > $O/r2_bench_qwen25_32b.json 2> $O/bench_qwen.err; echo "bench qwen rc=$?"
