@@ -6,6 +6,7 @@ nothing is copied into the repository's history) to sourceless byte code under `
     /root/reference/model_utils.py    -> oracle/_ref/model_utils.bin
     /root/reference/vector_utils.py   -> oracle/_ref/vector_utils.bin
     /root/reference/steering_utils.py -> oracle/_ref/steering_utils.bin
+    /root/reference/eval_utils.py, detect_injected_thoughts.py -> likewise (the driver, for the drop-in test)
 
 (`.pyc` content under another suffix: the snapshot that carries the tree to the GPU box leaves `*.pyc` files behind) —
 which is git-ignored but travels to the GPU box with the tree, like the built `libia_b200.so`.  There,
@@ -24,7 +25,7 @@ import sys
 REFERENCE = "/root/reference"
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "_ref")
-MODULES = ("model_utils", "vector_utils", "steering_utils")
+MODULES = ("model_utils", "vector_utils", "steering_utils", "eval_utils", "detect_injected_thoughts")
 
 
 def build(verbose: bool = True) -> bool:

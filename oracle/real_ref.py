@@ -73,14 +73,14 @@ def ids_to_prompts(ids: torch.Tensor, mask: torch.Tensor) -> List[str]:
     return [" ".join(str(int(t)) for t in row[m.bool()]) for row, m in zip(ids, mask)]
 
 
-def wrap(model, device: str, dtype: torch.dtype):
+def wrap(model, device: str, dtype: torch.dtype, tokenizer=None, model_name: str = "synthetic"):
     """The reference's ModelWrapper around `model` (reference model_utils.py:56-137, minus the Hub download)."""
     mu, _ = load()
     w = mu.ModelWrapper.__new__(mu.ModelWrapper)
-    w.model_name, w.hf_path = "synthetic", "synthetic"
+    w.model_name, w.hf_path = model_name, model_name
     w.device, w.dtype = device, dtype
     w.model = model
-    w.tokenizer = IdTokenizer(vocab_size=model.config.vocab_size)
+    w.tokenizer = tokenizer if tokenizer is not None else IdTokenizer(vocab_size=model.config.vocab_size)
     w.hooks = []
     w.n_layers = w._get_n_layers()
     return w
@@ -100,3 +100,61 @@ def steered_generate(w, ids, mask, layer_idx: int, vectors: Sequence[torch.Tenso
     return w.generate_batch_with_multi_steering(
         prompts=ids_to_prompts(ids, mask), layer_idx=layer_idx, steering_vectors=list(vectors), strength=strength,
         max_new_tokens=max_new_tokens, temperature=0.0, steering_start_positions=list(start_positions))
+
+
+def load_driver(bind: dict):
+    """The reference's sweep driver (detect_injected_thoughts.py, compiled into oracle/_ref) imported with the names
+    `model_utils` / `vector_utils` / `steering_utils` bound to the modules in `bind` — the real reference's own, or this
+    package's (INTEGRATION.md level 1: the import swap).  Plotting / judge dependencies that are not installed
+    (matplotlib, openai, dotenv) are stubbed: the sweep itself uses none of them with --no-llm-judge.  Returns the
+    driver module, or None when oracle/_ref does not hold it."""
+    import types
+
+    if not os.path.exists(os.path.join(REF_DIR, "detect_injected_thoughts.bin")) or load() is None:
+        return None
+    saved = {k: sys.modules.get(k) for k in ("model_utils", "vector_utils", "steering_utils", "eval_utils", "matplotlib",
+                                             "matplotlib.pyplot", "seaborn", "openai", "dotenv")}
+    try:
+        for name in ("matplotlib", "matplotlib.pyplot", "seaborn", "openai", "dotenv"):
+            try:
+                __import__(name)
+            except Exception:
+                stub = types.ModuleType(name)
+                stub.use = lambda *a, **k: None
+                stub.load_dotenv = lambda *a, **k: None
+                stub.AsyncOpenAI = stub.OpenAI = object
+                sys.modules[name] = stub
+        if "matplotlib.pyplot" in sys.modules:
+            sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+        for k, mod in bind.items():
+            sys.modules[k] = mod
+        _load_one("eval_utils")
+        drv = _load_one("detect_injected_thoughts")
+        sys.modules.pop("detect_injected_thoughts", None)
+        for name in ("create_sweep_plots", "create_cross_model_comparison_plots", "extract_example_transcripts"):
+            setattr(drv, name, lambda *a, **k: None)  # reporting only
+        return drv
+    finally:
+        for k, v in saved.items():
+            if v is not None:
+                sys.modules[k] = v
+            else:
+                sys.modules.pop(k, None)
+
+
+def load_steering_utils():
+    """The real reference's steering_utils (needs `model_utils` importable while it loads)."""
+    mods = load()
+    if mods is None:
+        return None
+    saved = sys.modules.get("model_utils")
+    sys.modules["model_utils"] = mods[0]
+    try:
+        su = _load_one("steering_utils")
+        sys.modules.pop("steering_utils", None)
+        return su
+    finally:
+        if saved is not None:
+            sys.modules["model_utils"] = saved
+        else:
+            sys.modules.pop("model_utils", None)
