@@ -302,23 +302,28 @@ __device__ __forceinline__ void cta_column_sum(const RowSource<T> &src, int laye
     }
 }
 
-// Fused path: n_base <= 256 (or RAW).  One CTA (4 warps; 4 CTAs per SM, so the 512 CTAs of a
-// 32-layer x 4096-column sweep are resident in a single wave) per (layer, tile).  Each warp's first batch
-// of concept rows is requested BEFORE the baseline rows are staged and summed: only the use of a
-// concept row depends on the mean, not its load, so both sets of loads share one memory round trip.
+// Fused path: n_base <= 256 (or RAW).  One CTA (4 warps, 4 CTAs per SM) per (layer, tile, share of the concept
+// rows).  Each warp's first batch of concept rows is requested BEFORE the baseline rows are staged and summed:
+// only the use of a concept row depends on the mean, not its load, so both sets of loads share one memory round
+// trip.  With `nsplit` > 1 (small problems only: fewer units than one wave) the concept rows of a (layer, tile) are
+// dealt over nsplit CTAs, each of which stages and sums the baseline rows itself (the same rows in the same order:
+// the same mean; the repeats are L2 hits), so that a few-layer extraction still fills the machine.
 template <typename T>
 __global__ void __launch_bounds__(128, 4) k1_fused_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
-                                                          int stage_rows, K1Out o) {
+                                                          int stage_rows, int nsplit, K1Out o) {
     extern __shared__ __align__(16) unsigned char smem[];
     float *mean_s = reinterpret_cast<float *>(smem);  // [2][kTileCols]: fp32 mean, rounded mean
     unsigned char *stage = smem + kMeanBytes;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int layer = blockIdx.x / o.ntiles;
-    const int tile = blockIdx.x - layer * o.ntiles;
+    const int split = blockIdx.x % nsplit;
+    const int unit = blockIdx.x / nsplit;
+    const int layer = unit / o.ntiles;
+    const int tile = unit - layer * o.ntiles;
     const int col = tile * kTileCols + lane * 8;
     const bool active = col < H;
+    const int64_t c0 = warp + (int64_t)nwarps * split, cstep = (int64_t)nwarps * nsplit;  // this warp's concept rows
     Raw8<T> first[RowBatch<T>::kRows];
-    load_batch<T>(csrc, layer, H, col, active, warp, nwarps, first);
+    load_batch<T>(csrc, layer, H, col, active, c0, cstep, first);
     float mean32[8], meanr[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) { mean32[i] = 0.f; meanr[i] = 0.f; }
@@ -341,9 +346,8 @@ __global__ void __launch_bounds__(128, 4) k1_fused_kernel(RowSource<T> csrc, Row
             meanr[i] = mean_s[kTileCols + lane * 8 + i];
         }
     }
-    emit_batch<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, warp, nwarps, first, o);
-    emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr,
-                 warp + (int64_t)nwarps * RowBatch<T>::kRows, nwarps, o);
+    emit_batch<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, c0, cstep, first, o);
+    emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, c0 + cstep * RowBatch<T>::kRows, cstep, o);
 }
 
 // Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.  Small CTAs
@@ -596,7 +600,12 @@ static int meandiff_t(const RowSource<T> &csrc, const RowSource<T> &bsrc, int L,
         static std::atomic<bool> done[64];
         const int rc = opt_in_smem(k1_fused_kernel<T>, done, kMeanBytes + kStageBytes);
         if (rc) return rc;
-        k1_fused_kernel<T><<<(unsigned)(L * ntiles), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, o);
+        // shares of the concept rows per (layer, tile): as many as still fit ONE wave of 4 CTAs per SM — measured on
+        // B200: one layer x 16 tiles 15.9 -> 13.1 us with 13 shares; the 32-layer sweep is already a full wave, and
+        // splitting it (3 shares, three times the baseline staging) costs 22.8 -> 30.0 us
+        const int64_t units = (int64_t)L * ntiles;
+        const int nsplit = (int)std::max<int64_t>(1, std::min<int64_t>((4 * 148) / units, std::max<int64_t>(1, (nc + 3) / 4)));
+        k1_fused_kernel<T><<<(unsigned)(units * nsplit), 128, smem, s>>>(csrc, bsrc, L, H, mode == IA_MODE_RAW, stage_rows, nsplit, o);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         if (!want_norm) return 0;  // nobody reads the norms
