@@ -151,6 +151,8 @@ class ModelWrapper:
     def extract_activations_multi(self, prompts: List[str], layer_indices: Sequence[int], token_idx: int = -1
                                   ) -> torch.Tensor:
         """[n_layers, B, H] CPU tensor in the model dtype: one forward for all layers."""
+        if self.engine.device.type != "cuda":
+            raise RuntimeError("activation capture runs inside the CUDA kernels (K2's tap); there is no CPU path")
         ids, mask = self._encode(prompts)
         return self.engine.capture_rows(ids, mask, layer_indices, token_idx).cpu()
 

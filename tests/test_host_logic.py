@@ -205,6 +205,8 @@ def test_hot_path_has_no_cpu_fallback(wrapper):
         wrapper.generate_with_steering("a b c", 1, v, strength=2.0, max_new_tokens=2)
     with pytest.raises(RuntimeError, match="no CPU path"):
         vu.extract_concept_vectors_batch(wrapper, ["Dust"], ["Sand", "Clay"], layer_idx=1)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        wrapper.extract_activations(["a b c"], 1)
     with pytest.raises(ValueError, match="Unknown extraction method"):
         vu.extract_concept_vectors_batch(wrapper, ["Dust"], ["Sand"], layer_idx=1, extraction_method="bogus")
     with pytest.raises(AssertionError, match="one steering vector per prompt"):
