@@ -113,7 +113,8 @@ def test_rope_append_matches_hf_rotary_plus_cache_update(dtype, B, T, nh, nkv, D
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
-@pytest.mark.parametrize("rows,width,fused", [(200, 14336, True), (7, 4864, False), (3, 256, True), (25600, 1024, False)])
+@pytest.mark.parametrize("rows,width,fused", [(200, 14336, True), (7, 4864, False), (3, 256, True), (25600, 1024, False),
+                                              (8192, 8192, True), (5000, 14336, False)])  # the last two: the table kernel (>= 64 M elements)
 def test_silu_mul_is_bit_identical_to_the_two_eager_kernels(dtype, rows, width, fused):
     if not torch.cuda.is_available():
         pytest.skip("needs a GPU")
