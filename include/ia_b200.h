@@ -305,6 +305,17 @@ IA_API int ia_rope_append(const void *q, const void *k, const void *v, int64_t q
 IA_API int ia_silu_mul(const void *gate, const void *up, void *out, int64_t rows, int64_t width, int64_t gate_row_stride,
                 int64_t up_row_stride, int32_t dtype, void *stream);
 
+/*
+ * Runtime support: out = round(table[gate] * up) over [rows, width] for a 16-bit dtype — `act_fn(gate_proj(x)) * up_proj(x)`
+ * of a gated MLP (transformers Gemma2MLP / LlamaMLP .forward) in one pass for ANY activation function: `table` holds
+ * act_fn of each of the 65 536 bit patterns of the dtype (index = the bit pattern; the caller fills it once by running
+ * its model's own act_fn on all of them), so the first rounding point is the library's own result and the second is
+ * the packed single-rounding multiply: bit-identical to the two eager kernels.  gate/up have their own row strides in
+ * elements, out is dense; width % 8 == 0; pointers 16-byte aligned.
+ */
+IA_API int ia_act_mul_table(const void *gate, const void *up, const void *table, void *out, int64_t rows, int64_t width,
+                     int64_t gate_row_stride, int64_t up_row_stride, int32_t dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -61,6 +61,7 @@ _SIGNATURES = {
                                c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
                                c_int32, c_void_p]),
     "ia_silu_mul": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32, c_void_p]),
+    "ia_act_mul_table": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32, c_void_p]),
 }
 IA_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024
 

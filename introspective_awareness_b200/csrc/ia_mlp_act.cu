@@ -134,6 +134,59 @@ template <typename T> static int launch_silu_mul_table(const void *gate, const v
     return (int)cudaGetLastError();
 }
 
+// out = RD(table[gate] * up): the gate activation looked up in a caller-supplied table of all 65 536 values of the
+// 16-bit dtype (128 KB, copied to shared memory by every CTA), then the packed single-rounding multiply.  The caller
+// fills the table with whatever its model's activation function returns for each bit pattern — e.g. ATen's tanh-GELU
+// for Gemma-2, whose fused-multiply-add contractions a hand-written GELU would have to mirror to reproduce its bits —
+// so the result is bit-identical to `act_fn(gate) * up` by construction.
+template <typename T>
+__global__ void __launch_bounds__(1024, 1) act_mul_table_kernel(const T *gate, const T *up, const unsigned short *table, T *out,
+                                                                long rows, int I, long g_rs, long u_rs) {
+    extern __shared__ __align__(16) unsigned short act_tab[];
+    for (unsigned i = threadIdx.x; i < 65536u / 8; i += blockDim.x)
+        reinterpret_cast<uint4 *>(act_tab)[i] = __ldg(reinterpret_cast<const uint4 *>(table) + i);
+    __syncthreads();
+    const int per_row = I / 8;
+    const long total = rows * per_row;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long r = i / per_row;
+        const int c = (int)(i - r * per_row) * 8;
+        const uint4 gv = *reinterpret_cast<const uint4 *>(gate + r * g_rs + c);
+        const uint4 uv = *reinterpret_cast<const uint4 *>(up + r * u_rs + c);
+        const unsigned gw[4] = {gv.x, gv.y, gv.z, gv.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w};
+        unsigned ow[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned s = (unsigned)act_tab[gw[k] & 0xffffu] | ((unsigned)act_tab[gw[k] >> 16] << 16);
+            ow[k] = mul2<T>(s, uw[k]);
+        }
+        *reinterpret_cast<uint4 *>(out + r * (long)I + c) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
+}
+
+template <typename T> static int launch_act_mul_table(const void *gate, const void *up, const void *table, void *out, long rows, int I,
+                                                      long g_rs, long u_rs, cudaStream_t st) {
+    static std::atomic<bool> done[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (!done[dev].load(std::memory_order_acquire)) {
+        cudaError_t e = cudaFuncSetAttribute(act_mul_table_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSiluTableBytes);
+        if (e != cudaSuccess) return (int)e;
+        done[dev].store(true, std::memory_order_release);
+    }
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // every CTA pays for a 128 KB table copy (an L2 hit after the first): small launches use fewer CTAs
+    const long per_cta = 1024L * 8 * 16;
+    long ctas = (rows * (long)I + per_cta - 1) / per_cta;
+    if (ctas > sms) ctas = sms;
+    if (ctas < 1) ctas = 1;
+    act_mul_table_kernel<T><<<(unsigned)ctas, 1024, kSiluTableBytes, st>>>(static_cast<const T *>(gate), static_cast<const T *>(up),
+                                                                          static_cast<const unsigned short *>(table),
+                                                                          static_cast<T *>(out), rows, I, g_rs, u_rs);
+    return (int)cudaGetLastError();
+}
+
 template <typename T>
 static int launch_silu_mul(const void *gate, const void *up, void *out, long rows, int I, long g_rs, long u_rs, cudaStream_t st) {
     constexpr int E = 16 / sizeof(T);
@@ -167,4 +220,20 @@ extern "C" int ia_silu_mul(const void *gate, const void *up, void *out, int64_t 
     case IA_F32: return launch_silu_mul<float>(gate, up, out, rows, (int)width, gate_row_stride, up_row_stride, st);
     default: return IA_ERR_DTYPE;
     }
+}
+
+extern "C" int ia_act_mul_table(const void *gate, const void *up, const void *table, void *out, int64_t rows, int64_t width,
+                                int64_t gate_row_stride, int64_t up_row_stride, int32_t dtype, void *stream) {
+    using namespace ia;
+    if (!gate || !up || !out || !table) return IA_ERR_NULL;
+    if (dtype != IA_BF16 && dtype != IA_F16) return IA_ERR_DTYPE;  // the table enumerates a 16-bit dtype
+    if (rows < 0 || width < 8 || width % 8 || width >= ((int64_t)1 << 31)) return IA_ERR_SHAPE;
+    if (gate_row_stride < width || up_row_stride < width) return IA_ERR_SHAPE;
+    if (gate_row_stride % 8 || up_row_stride % 8 || !aligned16(gate) || !aligned16(up) || !aligned16(out) || !aligned16(table))
+        return IA_ERR_ALIGN;
+    if (rows == 0) return 0;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == IA_BF16)
+        return launch_act_mul_table<__nv_bfloat16>(gate, up, table, out, rows, (int)width, gate_row_stride, up_row_stride, st);
+    return launch_act_mul_table<__half>(gate, up, table, out, rows, (int)width, gate_row_stride, up_row_stride, st);
 }

@@ -265,6 +265,12 @@ class DecoderEngine:
                              and all(hasattr(first.mlp, n) for n in ("gate_proj", "up_proj", "down_proj")))
         self.fuse_projections = True
         self.gemma_tail_everywhere = True   # Gemma-2: block-tail K2 at both residual joins of every layer
+        # Gemma-2's gated MLP driven from here: gate/up as one GEMM where that is bit-identical, GELU(gate) * up in one
+        # pass through a table of the module's own act_fn over all 65 536 values of the dtype (`_mlp_table`)
+        self.table_mlp = (self.device.type == "cuda" and self.is_gemma2 and self.dtype in (torch.bfloat16, torch.float16)
+                          and getattr(cfg, "intermediate_size", 0) % 8 == 0
+                          and all(hasattr(first.mlp, n) for n in ("gate_proj", "up_proj", "down_proj", "act_fn")))
+        self._act_table: Optional[torch.Tensor] = None
         self._qkv: Optional[list] = None   # per layer _FusedLinear, built on first use
         self._gu: Optional[list] = None
         self._fused_checked: Dict[tuple, bool] = {}
@@ -519,6 +525,21 @@ class DecoderEngine:
         self.counters["act_launches"] += 1
         return mlp.down_proj(kernels.silu_mul(g, u))
 
+    def _mlp_table(self, layer, i: int, x: torch.Tensor) -> torch.Tensor:
+        """transformers' Gemma2MLP.forward — down_proj(act_fn(gate_proj(x)) * up_proj(x)) — with the same GEMMs and the
+        two eager elementwise kernels replaced by one table pass: the table is the module's own act_fn (ATen's
+        tanh-GELU) evaluated on every value of the dtype, so both rounding points keep their bits."""
+        mlp = layer.mlp
+        if self._act_table is None:
+            with torch.inference_mode(False):  # an ordinary tensor: it outlives this call
+                self._act_table = kernels.activation_table(mlp.act_fn, self.dtype, self.device)
+        if self._fused_ok("gu", x.shape):
+            g, u = self._gu[i](x)
+        else:
+            g, u = mlp.gate_proj(x), mlp.up_proj(x)
+        self.counters["act_launches"] += 1
+        return mlp.down_proj(kernels.act_mul_table(g, u, self._act_table))
+
     def _k2(self, h, weight, add=None, steer: Optional[SteerSpec] = None, pos0: int = 0, decode: bool = False,
             timed: bool = False, cap_out: Optional[torch.Tensor] = None, cap_t: int = -1):
         ev = None
@@ -573,7 +594,7 @@ class DecoderEngine:
             attn, _ = layer.self_attn(hidden_states=x, position_embeddings=pos_emb,
                                       attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
             x = self._gemma_tail(attn, h, layer.post_attention_layernorm.weight, layer.pre_feedforward_layernorm.weight)
-            m = layer.mlp(x)
+            m = self._mlp_table(layer, i, x) if self.table_mlp else layer.mlp(x)
             st = steer.at(i) if steer is not None else None
             nxt = self.layers[i + 1].input_layernorm if i + 1 < self.n_layers else self.inner.norm
             if i == last and stop_after is not None and st is None and i in captured:

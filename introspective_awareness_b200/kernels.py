@@ -353,3 +353,28 @@ def silu_mul(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
     rc = _lib.load().ia_silu_mul(gp, up_p, out.data_ptr(), rows, width, grs, urs, _dt(gate), _stream())
     check(rc, "ia_silu_mul")
     return out
+
+
+def activation_table(act_fn, dtype: torch.dtype, device) -> torch.Tensor:
+    """act_fn of every one of the 65 536 values of a 16-bit dtype, indexed by bit pattern: the table `act_mul_table`
+    looks the gate activation up in.  Computed by the model's own activation module on the device, so its entries are
+    that library's bits (NaN patterns included)."""
+    if dtype not in (torch.bfloat16, torch.float16):
+        raise TypeError("activation tables enumerate a 16-bit dtype")
+    bits = torch.arange(65536, dtype=torch.int32, device=device).to(torch.int16)  # 0..65535 wraps to the same bit patterns
+    with torch.no_grad():
+        return act_fn(bits.view(dtype)).contiguous()
+
+
+def act_mul_table(gate: torch.Tensor, up: torch.Tensor, table: torch.Tensor) -> torch.Tensor:
+    """round(table[gate] * up) in one pass; gate / up [..., I] dense or column slices of one tensor, 16-bit dtype."""
+    width = gate.shape[-1]
+    gp, grs = _rows_view(gate, width, "gate")
+    up_p, urs = _rows_view(up, width, "up")
+    if up.shape != gate.shape or up.dtype != gate.dtype or table.dtype != gate.dtype or table.numel() != 65536:
+        raise ValueError("gate, up and the 65536-entry table must share a 16-bit dtype")
+    out = torch.empty(gate.shape, dtype=gate.dtype, device=gate.device)
+    rows = out.numel() // width
+    rc = _lib.load().ia_act_mul_table(gp, up_p, _cuda(table, "table"), out.data_ptr(), rows, width, grs, urs, _dt(gate), _stream())
+    check(rc, "ia_act_mul_table")
+    return out

@@ -307,7 +307,7 @@ def test_sweep_driver_end_to_end(tmp_path):
     assert texts == [r["response"] for r in inj]
 
 
-@pytest.mark.parametrize("arch", ["tiny-llama", "tiny-gemma2", "llama-8b-4layer"])
+@pytest.mark.parametrize("arch", ["tiny-llama", "tiny-gemma2", "llama-8b-4layer", "gemma-2-9b-4layer"])
 def test_runtime_optimisations_do_not_change_bits(arch):
     """K2 for every RMSNorm, the fused rotary kernel, the Gemma-2 tail variant, grouped-query SDPA, the
     CUDA graphs, the once-per-forward mask conversion, the engine-driven Llama block (residual add inside K2,
@@ -335,7 +335,7 @@ def test_runtime_optimisations_do_not_change_bits(arch):
     if eng.native_block:  # Llama / Qwen2: the block driven by the engine vs the HF layer forwards
         settings += [("native_block", False), ("fuse_projections", False)]
     if eng.is_gemma2:
-        settings += [("fuse_gemma_tail", False), ("gemma_tail_everywhere", False)]
+        settings += [("fuse_gemma_tail", False), ("gemma_tail_everywhere", False), ("table_mlp", False), ("fuse_projections", False)]
     else:
         settings.append(("attention", "gqa"))
     for name, value in settings:

@@ -177,3 +177,30 @@ def test_one_set_of_decode_graphs_serves_every_layer_and_sessions_are_kept(arch)
     w.steered_generate_ids(ids[:, -27:], mask[:, -27:], 1, table, row_vec, [4.0] * rows, [max(0, t - 3) for t in t0], 10)
     assert len(w.engine._sessions) == 3 and first in w.engine._sessions.values()          # the width-29 session went
     assert [k[1] for k in w.engine._sessions] == [28, 30, 27]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("rows,width,fused", [(200, 14336, True), (7, 4864, False), (3, 256, True), (6000, 14336, False)])
+def test_table_activation_gate_multiply_is_bit_identical_to_the_eager_kernels(dtype, rows, width, fused):
+    """ia_act_mul_table with the table filled by ATen's own tanh-GELU (Gemma-2) and SiLU: act_fn(gate) * up, bit for
+    bit, small launches (few CTAs) and large ones, dense operands or the two halves of one fused projection output."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from introspective_awareness_b200 import kernels
+
+    dev = "cuda:0"
+    g = torch.Generator(device=dev).manual_seed(rows + width)
+    gu = (torch.randn(rows, 2 * width, device=dev, generator=g) * 4).to(dtype)
+    gu[0, :8] = torch.tensor([0.0, -0.0, 30.0, -30.0, 88.0, -88.0, 1e-3, -1e-3], device=dev).to(dtype)
+    gu[0, 8:11] = torch.tensor([float("inf"), float("-inf"), float("nan")], device=dev).to(dtype)
+    gate, up = gu.split(width, dim=-1)
+    if not fused:
+        gate, up = gate.contiguous(), up.contiguous()
+    for act in (torch.nn.GELU(approximate="tanh"), torch.nn.SiLU()):
+        table = kernels.activation_table(act, dtype, dev)
+        assert table.shape == (65536,) and table.dtype == dtype
+        want = act(gate) * up
+        got = kernels.act_mul_table(gate, up, table)
+        torch.cuda.synchronize()
+        assert got.is_contiguous()
+        assert torch.equal(got.view(torch.int16), want.view(torch.int16)), type(act).__name__   # bit patterns, NaNs included
