@@ -206,3 +206,40 @@ def test_table_activation_gate_multiply_is_bit_identical_to_the_eager_kernels(dt
         nan = want.isnan()
         assert torch.equal(got.isnan(), nan), type(act).__name__
         assert torch.equal(got.view(torch.int16)[~nan], want.view(torch.int16)[~nan]), type(act).__name__  # bit patterns
+
+
+def test_generation_config_settings_inside_the_decode_graphs():
+    """Repetition penalty (a Qwen2.5-Instruct default, applied to greedy decoding too) and an EOS *set* whose second id
+    fires, on the GPU where the decode steps are CUDA graphs: same tokens as HF `generate` with the same
+    generation_config, for steered rows as for plain ones (the penalty buffer and the EOS ids live in the graphs)."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from introspective_awareness_b200.model_utils import ModelWrapper
+    from introspective_awareness_b200.synthetic import synthetic_prompt_ids
+    from oracle import ref_hooks
+
+    w = ModelWrapper.from_arch("tiny-llama", device="cuda:0", dtype=torch.bfloat16, seed=41)
+    V = w.model.config.vocab_size
+    ids, mask, lens = synthetic_prompt_ids(10, 24, 14, V, seed=6)
+    gc_ = w.model.generation_config
+    gc_.repetition_penalty = 1.3
+    with torch.no_grad():
+        free = w.model.generate(input_ids=ids.cuda(), attention_mask=mask.cuda(), max_new_tokens=12, do_sample=False, pad_token_id=0)
+    fires = int(free[0, 24 + 4])  # row 0's fifth new token becomes an end-of-sequence id
+    gc_.eos_token_id = [V - 1, fires]
+    try:
+        with torch.no_grad():
+            ref = w.model.generate(input_ids=ids.cuda(), attention_mask=mask.cuda(), max_new_tokens=12, do_sample=False, pad_token_id=0)
+        got = w.steered_generate_ids(ids, mask, None, None, None, None, None, 12)
+        new = ref[:, 24:]
+        assert torch.equal(got[:, : new.shape[1]], new) and (got[:, new.shape[1]:] == 0).all()
+        assert int(got[0, 4]) == fires and (got[0, 5:] == 0).all()
+        # steered rows under the same settings: the hook path through HF generate
+        table = (torch.randn(3, w.engine.hidden, generator=torch.Generator().manual_seed(1)) * 0.5).to(torch.bfloat16)
+        row_vec = [i % 3 for i in range(10)]
+        t0 = (lens - 6).tolist()
+        want = ref_hooks.steered_generate(w.model, ids, mask, 1, [table[j] for j in row_vec], 4.0, t0, 12)["new_ids"]
+        mine = w.steered_generate_ids(ids, mask, 1, table, row_vec, [4.0] * 10, t0, 12).cpu()
+        assert torch.equal(mine[:, : want.shape[1]], want) and (mine[:, want.shape[1]:] == 0).all()
+    finally:
+        gc_.repetition_penalty, gc_.eos_token_id = 1.0, None
