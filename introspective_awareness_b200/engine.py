@@ -835,6 +835,7 @@ class Session:
         penalty when positive and multiplied by it when negative (applies to greedy decoding too)."""
         if penalty == 1.0:
             return lg
+        lg = lg.float()  # HF runs its logits processors on an fp32 copy of the last-position logits
         seen = lg.gather(1, self.hist)
         seen = torch.where(seen < 0, seen * penalty, seen / penalty)
         return lg.scatter(1, self.hist, seen)
