@@ -405,7 +405,8 @@ def measure_other_arch(arch, args, rank, world, local) -> dict:
         return {"metric": metric_name(arch), "value": arm.rows * world * 3 / (ms / 1e3), "unit": UNIT, "ms_per_step": ms / 3, "steps": 3,
                 "warmup": 3, "layers": arm.sweep, "rows_per_gpu_per_step": arm.rows, "n_gpus": world,
                 "k2_prompt_pass_us": (sum(k2_ms) / len(k2_ms) * 1e3) if k2_ms else None,
-                "engine_block": "native" if arm.eng.native_block else "hf", "attention": arm.eng.attention}
+                "engine_block": "native" if (arm.eng.native_block or arm.eng.gemma_native_attention) else "hf",
+                "attention": arm.eng.attention}
     finally:
         arm.free()
 
@@ -513,6 +514,8 @@ def run_ours(args):
         cpu = cpu_baseline_port(arm.model, arm.my_layer, arm.wl, sample_rows=args.cpu_rows)
 
     sweep, fused, attention, native = arm.sweep, dict(eng._fused_checked), eng.attention, eng.native_block
+    block_kind = ("gemma-2: engine attention + table MLP + block-tail K2" if getattr(eng, "gemma_native_attention", False) and eng.table_mlp
+                  else "hf")
     arm_sharded = arm.sharded_extraction
     if (world == 8 or args.other_archs) and arch == ARCH and not args.no_extras:
         del eng
@@ -529,7 +532,7 @@ def run_ours(args):
                             f"layer, one {rows}-row steered batch per GPU, prompt {T_PROMPT} (real {T_MIN}..{T_PROMPT}, "
                             f"left-padded), {N_NEW} greedy tokens, extraction {N_CONCEPTS}+{N_BASE} prompts per step",
                 "layers": sweep, "rows_per_gpu_per_step": rows, "new_tokens": N_NEW, "attention": attention,
-                "engine_block": "native" if native else "hf",
+                "engine_block": "native" if native else block_kind,
                 "single_gemm_projections": {f"{k}{list(shape)}": ok for (k, shape), ok in sorted(fused.items())},
                 "parallelism": ("independent replicas, layer axis round-robin; extraction "
                                 + ("prompt-sharded (NCCL all-reduce / all-gather)" if arm_sharded else "from the whole prompt sets on every rank")

@@ -271,6 +271,11 @@ class DecoderEngine:
                           and getattr(cfg, "intermediate_size", 0) % 8 == 0
                           and all(hasattr(first.mlp, n) for n in ("gate_proj", "up_proj", "down_proj", "act_fn")))
         self._act_table: Optional[torch.Tensor] = None
+        # ... and its attention block: Gemma2Attention.forward is LlamaAttention.forward plus two keyword arguments
+        # for the attention function, so `_attn_native` serves it (one q/k/v GEMM where bit-identical, rotary + KV
+        # append in one launch, the sliding layers' key window on cached steps)
+        self.gemma_native_attention = (self.device.type == "cuda" and self.is_gemma2 and self.head_dim % 16 == 0
+                                       and all(hasattr(first.self_attn, n) for n in ("q_proj", "k_proj", "v_proj", "o_proj", "scaling")))
         self._qkv: Optional[list] = None   # per layer _FusedLinear, built on first use
         self._gu: Optional[list] = None
         self._fused_checked: Dict[tuple, bool] = {}
@@ -512,7 +517,10 @@ class DecoderEngine:
         qr = kernels.rope_append(q, k, v, cos.contiguous(), sin.contiguous(), kd, vd, pos, nh, nkv, d)
         self.counters["rope_launches"] += 1
         extra = {"sliding_window": att.sliding_window} if hasattr(att, "sliding_window") else {}
-        out, _ = self._attention_fn()(att, qr, kd[:, :, :end], vd[:, :, :end], mask, dropout=0.0, scaling=att.scaling,
+        if hasattr(att, "attn_logit_softcapping"):  # Gemma2Attention.forward hands it to the attention function
+            extra["softcap"] = att.attn_logit_softcapping
+        lo = cache.window_start(i, t, end) if cache is not None else 0  # Gemma-2 sliding layers on cached steps
+        out, _ = self._attention_fn()(att, qr, kd[:, :, lo:end], vd[:, :, lo:end], mask, dropout=0.0, scaling=att.scaling,
                                       **extra)
         return att.o_proj(out.reshape(b, t, -1))
 
@@ -591,8 +599,11 @@ class DecoderEngine:
         final = None
         for i in range(last + 1):
             layer = self.layers[i]
-            attn, _ = layer.self_attn(hidden_states=x, position_embeddings=pos_emb,
-                                      attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
+            if self.gemma_native_attention:
+                attn = self._attn_native(layer, i, x, pos_emb, masks[self._layer_kind(i)], cache)
+            else:
+                attn, _ = layer.self_attn(hidden_states=x, position_embeddings=pos_emb,
+                                          attention_mask=masks[self._layer_kind(i)], past_key_values=cache)
             x = self._gemma_tail(attn, h, layer.post_attention_layernorm.weight, layer.pre_feedforward_layernorm.weight)
             m = self._mlp_table(layer, i, x) if self.table_mlp else layer.mlp(x)
             st = steer.at(i) if steer is not None else None

@@ -335,7 +335,8 @@ def test_runtime_optimisations_do_not_change_bits(arch):
     if eng.native_block:  # Llama / Qwen2: the block driven by the engine vs the HF layer forwards
         settings += [("native_block", False), ("fuse_projections", False)]
     if eng.is_gemma2:
-        settings += [("fuse_gemma_tail", False), ("gemma_tail_everywhere", False), ("table_mlp", False), ("fuse_projections", False)]
+        settings += [("fuse_gemma_tail", False), ("gemma_tail_everywhere", False), ("table_mlp", False), ("fuse_projections", False),
+                     ("gemma_native_attention", False)]
     else:
         settings.append(("attention", "gqa"))
     for name, value in settings:
