@@ -340,3 +340,34 @@ def test_gemma2_sliding_window_steps_match_hf_generate():
     theirs = torch.stack([l.float() for l in ref.logits])
     assert torch.equal(got, ref.sequences[:, 60:])
     assert (ours - theirs).abs().max().item() <= 1e-4
+
+
+def test_sessions_are_kept_least_recently_used_first_out(wrapper):
+    """The runtime keeps the static buffers of the last few batch shapes (a sweep alternates between a handful);
+    a fourth shape evicts the least recently used one; `_session = None` drops them all."""
+    eng = wrapper.engine
+    eng._session = None
+    made = {}
+    for width in (5, 6, 7):
+        made[width] = eng.session(2, width, 4, padded=True)
+    assert list(k[1] for k in eng._sessions) == [5, 6, 7] and eng._session is made[7]
+    assert eng.session(2, 5, 4, padded=True) is made[5]          # a hit moves the shape to the most recent end
+    eng.session(2, 8, 4, padded=True)                           # the least recently used one (6) goes
+    assert list(k[1] for k in eng._sessions) == [7, 5, 8]
+    assert eng.session(2, 6, 4, padded=True) is not made[6]
+    eng._session = None
+    assert not eng._sessions and eng._session is None
+
+
+def test_steer_spec_per_layer_rows():
+    from introspective_awareness_b200.engine import SteerSpec
+
+    table = torch.zeros(3, 8)
+    one = SteerSpec(2, table, torch.tensor([0, 1], dtype=torch.int32), torch.ones(2), None)
+    assert one.at(2) is one and one.at(1) is None
+    rows = torch.full((4, 2), -1, dtype=torch.int32)
+    rows[2] = torch.tensor([0, 1])
+    every = SteerSpec(None, table, rows, torch.ones(2), None)
+    for i in range(4):
+        s = every.at(i)
+        assert s.layer_idx == i and torch.equal(s.row_vec, rows[i]) and s.vtable is table
