@@ -62,7 +62,10 @@ def test_against_real_reference_outputs(name):
     want = torch.from_numpy(widen(g["vectors"], dtn))
     got = vr[0].float().cpu()
     rel = ((got - want).norm(dim=1) / want.norm(dim=1)).max().item()
-    assert rel <= (1e-3 if dtn == "f32" else 2e-2), rel  # bf16: CPU-vs-GPU GEMM rounding upstream of K1
+    # bf16 fixtures were computed on a CPU: its GEMM rounding differs from the GPU's upstream of K1, hence 2e-2 here; the
+    # 1e-3 bound of north_star (in fact: identical bits) is asserted where both sides run on the same device —
+    # test_same_device_extraction_against_the_hook_path and tests/test_real_reference_bridge.py
+    assert rel <= (1e-3 if dtn == "f32" else 2e-2), rel
     # steering with the REFERENCE's vectors, so this half does not inherit extraction differences
     table = want.to(DT[dtn])
     t0 = None if bool(g["steer_all"]) else g["t0"].tolist()
