@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <type_traits>
 #include <mutex>
 
 #include "ia_common.cuh"
@@ -350,6 +351,146 @@ __global__ void __launch_bounds__(128, 4) k1_fused_kernel(RowSource<T> csrc, Row
     emit_rows<T>(csrc, layer, tile, lane, H, col, active, raw != 0, mean32, meanr, c0 + cstep * RowBatch<T>::kRows, cstep, o);
 }
 
+// ---- column-walker path -------------------------------------------------------------------------
+// The same arithmetic with no shared memory, no barrier and no idle warp, for calls with many columns.  A THREAD owns
+// four bytes of a row (two 16-bit columns or one fp32 column: a warp reads one full 128-byte line per load) of one
+// layer, requests kWalkRows baseline rows at a time into registers, adds them in row order, and then walks the concept
+// rows the same way.  The summation order is a per-column contract, so columns are the only parallelism on offer —
+// n_layers * H * sizeof(T) / 4 threads.  For a whole sweep (32 x 4096 bf16: 2048 warps, ~14 per SM, each with 50
+// line-sized loads outstanding) that keeps HBM busier than the staged kernel above, in which one warp in four adds
+// while the others wait at a barrier; a few-layer call stays on the staged kernel, which splits the concept rows of a
+// column over CTAs.  Used when nobody reads the squared-norm partials (the production call: SURVEY.md A7, the driver
+// never normalises).  Measured on B200, cold L2, 50 concepts x 100 baseline rows, bf16 (tools/k1_walk_probe.py):
+//      layers x H      staged     walker
+//       1 x 4096      10.4 us    12.4 us
+//       8 x 4096      14.1       14.3
+//      28 x 3584      20.4       16.4 - 18.1
+//      32 x 4096      22.6       19.4 - 20.9
+//      64 x 5120      49.3       39.0 - 41.3
+// Deeper variants measured and dropped: 25 / 32 / 64 rows per request (20.2 / 22.5 / 25.0 us at 32 x 4096), the next
+// request issued before the current rows are used (20.6), eight bytes per thread (20.7), and all 150 rows of a thread
+// requested at once through cp.async into a private shared-memory column (22.2).
+constexpr int kWalkRows = 50;
+constexpr int64_t kWalkMinColumns = 65536;  // n_layers * H from which the walker is used (16 layers x 4096)
+
+template <typename T> __device__ __forceinline__ void walk_widen(uint32_t r, float (&f)[4 / sizeof(T)]) {
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        f[0] = __uint_as_float(r << 16);
+        f[1] = __uint_as_float(r & 0xffff0000u);
+    } else if constexpr (std::is_same<T, __half>::value) {
+        const __half2 h = *reinterpret_cast<const __half2 *>(&r);
+        f[0] = __low2float(h);
+        f[1] = __high2float(h);
+    } else {
+        f[0] = __uint_as_float(r);
+    }
+}
+// f[] already rounded to T (outputs of Elt<T>::rd)
+template <typename T> __device__ __forceinline__ uint32_t walk_pack(const float (&f)[4 / sizeof(T)]) {
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        return (__float_as_uint(f[0]) >> 16) | (__float_as_uint(f[1]) & 0xffff0000u);
+    } else if constexpr (std::is_same<T, __half>::value) {
+        const __half2 h = __floats2half2_rn(f[0], f[1]);
+        return *reinterpret_cast<const uint32_t *>(&h);
+    } else {
+        return __float_as_uint(f[0]);
+    }
+}
+
+// One thread's view of a segment's rows in one layer.  Compact rows and rows gathered WITHOUT index arrays (row r of a
+// [n, T, H] tensor at its last position) are a fixed stride apart; calls with row / token index arrays stay on the
+// staged kernel, where a warp, not every thread, reads the indices.
+template <typename T> struct WalkRows {
+    const T *first;  // this thread's column group of row 0
+    int64_t stride;  // elements between consecutive rows
+    int64_t n;
+    __device__ __forceinline__ WalkRows(const RowSource<T> &src, int layer, int H, int col) : n(src.n) {
+        if (src.ptrs) {
+            first = static_cast<const T *>(src.ptrs[layer]) + (src.T_len - 1) * (int64_t)H + col;
+            stride = src.T_len * (int64_t)H;
+        } else {
+            first = src.compact + (int64_t)layer * src.n * H + col;
+            stride = H;
+        }
+    }
+    __device__ __forceinline__ const uint32_t *at(int64_t r) const { return reinterpret_cast<const uint32_t *>(first + r * stride); }
+};
+
+// kWalkRows rows r0.. of one column group, requested together; rows past the end are left untouched (and unused).
+template <typename T> __device__ __forceinline__ void walk_request(const WalkRows<T> &rows, int64_t r0, uint32_t (&buf)[kWalkRows]) {
+    if (r0 + kWalkRows <= rows.n) {
+#pragma unroll
+        for (int u = 0; u < kWalkRows; ++u) buf[u] = __ldg(rows.at(r0 + u));
+    } else {
+#pragma unroll
+        for (int u = 0; u < kWalkRows; ++u)
+            if (r0 + u < rows.n) buf[u] = __ldg(rows.at(r0 + u));
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128) k1_walk_kernel(RowSource<T> csrc, RowSource<T> bsrc, int n_layers, int H, int raw,
+                                                      float *out_f32, T *out_rounded) {
+    constexpr int kN = 4 / (int)sizeof(T);  // columns per thread
+    const int per_layer = H / kN;
+    const int64_t unit = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (unit >= (int64_t)n_layers * per_layer) return;  // no barrier and no warp-wide operation below
+    const int layer = (int)(unit / per_layer);
+    const int col = (int)(unit - (int64_t)layer * per_layer) * kN;
+    float mean32[kN], meanr[kN];
+#pragma unroll
+    for (int i = 0; i < kN; ++i) { mean32[i] = 0.f; meanr[i] = 0.f; }
+    uint32_t buf[kWalkRows];
+    if (!raw) {
+        const int64_t nb = bsrc.n;
+        const WalkRows<T> rows(bsrc, layer, H, col);
+        float sum[kN];
+#pragma unroll
+        for (int i = 0; i < kN; ++i) sum[i] = 0.f;
+#pragma unroll 1
+        for (int64_t r0 = 0; r0 < nb; r0 += kWalkRows) {
+            walk_request<T>(rows, r0, buf);
+#pragma unroll
+            for (int u = 0; u < kWalkRows; ++u) {
+                if (r0 + u < nb) {
+                    float a[kN];
+                    walk_widen<T>(buf[u], a);
+#pragma unroll
+                    for (int i = 0; i < kN; ++i) sum[i] = __fadd_rn(sum[i], a[i]);
+                }
+            }
+        }
+        const float n = (float)nb;
+#pragma unroll
+        for (int i = 0; i < kN; ++i) {
+            mean32[i] = __fdiv_rn(sum[i], n);
+            meanr[i] = Elt<T>::rd(mean32[i]);
+        }
+    }
+    const int64_t nc = csrc.n;
+    const WalkRows<T> rows(csrc, layer, H, col);
+    const int64_t obase = (int64_t)layer * nc * H + col;
+#pragma unroll 1
+    for (int64_t c0 = 0; c0 < nc; c0 += kWalkRows) {
+        walk_request<T>(rows, c0, buf);
+#pragma unroll
+        for (int u = 0; u < kWalkRows; ++u) {
+            if (c0 + u < nc) {
+                float a[kN], vr[kN];
+                walk_widen<T>(buf[u], a);
+#pragma unroll
+                for (int i = 0; i < kN; ++i) vr[i] = raw ? a[i] : Elt<T>::rd(__fsub_rn(a[i], meanr[i]));
+                const int64_t off = obase + (c0 + u) * (int64_t)H;
+                if (out_f32) {
+#pragma unroll
+                    for (int i = 0; i < kN; ++i) out_f32[off + i] = raw ? a[i] : __fsub_rn(a[i], mean32[i]);
+                }
+                *reinterpret_cast<uint32_t *>(out_rounded + off) = walk_pack<T>(vr);
+            }
+        }
+    }
+}
+
 // Chunked column sums: one CTA per (chunk, layer, tile); also the rank-local gather.  Small CTAs
 // (4 warps, 32 KB of staging) so that ~7 are resident per SM: a CTA's start-up and drain (pointer
 // table -> first rows -> last adds -> store), during which it has no loads in flight, is then
@@ -517,6 +658,15 @@ template <typename K> static int opt_in_smem(K kern, std::atomic<bool> (&done)[6
     return 0;
 }
 
+template <typename T>
+static int launch_walk(const RowSource<T> &csrc, const RowSource<T> &bsrc, int L, int H, int raw, float *out_f32, T *out_rounded,
+                       cudaStream_t s) {
+    const int64_t units = (int64_t)L * (H / (4 / (int)sizeof(T)));
+    const unsigned grid = (unsigned)((units + 127) / 128);
+    k1_walk_kernel<T><<<grid, 128, 0, s>>>(csrc, bsrc, L, H, raw, out_f32, out_rounded);
+    return (int)cudaGetLastError();
+}
+
 static inline int64_t up64(int64_t x) { return (x + 63) / 64 * 64; }  // floats -> 256-byte multiples
 static inline int nchunks_of(int64_t n) { return (int)((n + kChunkRows - 1) / kChunkRows); }
 
@@ -591,6 +741,9 @@ static int meandiff_t(const RowSource<T> &csrc, const RowSource<T> &bsrc, int L,
     const int64_t n_out = mode == IA_MODE_POSNEG ? 1 : nc;
     if (mode != IA_MODE_POSNEG && (mode == IA_MODE_RAW || nb <= kChunkRows)) {
         const bool want_norm = normalize || out_norm;
+        const bool indexed = csrc.row || csrc.tok || (mode != IA_MODE_RAW && (bsrc.row || bsrc.tok));
+        if (!want_norm && !indexed && (int64_t)L * H >= kWalkMinColumns)
+            return launch_walk<T>(csrc, bsrc, L, H, mode == IA_MODE_RAW, out_f32, static_cast<T *>(out_rounded), s);
         // all baseline rows in one pass when they fit half the staging budget each way (two halves of
         // `stage_rows` rows), otherwise two alternating half-size passes
         const int row_bytes = kTileCols * (int)sizeof(T);

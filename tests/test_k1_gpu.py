@@ -192,3 +192,52 @@ def test_compact_entry_bit_exact_against_oracle_and_gathered(dt, mode):
             s = kernels.segsum_compact(bt)
             for l in range(L):
                 assert np.array_equal(s[l].cpu().numpy(), K.column_sum(base[l])), (dt, k, l)
+
+
+@pytest.mark.parametrize("dt", ["bf16", "f16", "f32"])
+@pytest.mark.parametrize("mode", ["baseline", "simple", "raw"])
+def test_column_walker_bit_exact_against_oracle_and_staged_kernel(dt, mode):
+    """Calls with n_layers * H >= 65536 and no norm outputs run the column-walker kernel (a thread per 4 bytes of a
+    row, 50 rows per request): the same bits as the oracle and as the staged kernel (the same call WITH norm outputs),
+    compact and gathered, for row counts on both sides of a request (49 / 50 / 51 / 101 / 256 rows)."""
+    from introspective_awareness_b200 import kernels
+
+    dev = _dev()
+    shapes = [(80, 7, 100, 896), (16, 50, 49, 4096), (20, 51, 256, 3584), (70, 101, 50, 1024)]
+    for k, (L, C, Nb, H) in enumerate(shapes):
+        assert L * H >= 65536
+        if mode == "simple":
+            Nb = 1
+        conc = residual_batch(L, C, 1, H, dt, 300 + k)[:, :, 0]
+        base = residual_batch(L, Nb, 1, H, dt, 400 + k)[:, :, 0]
+        ct, bt = to_model(conc, dt, dev), to_model(base, dt, dev)
+        bt_arg = None if mode == "raw" else bt
+        w32, wr, none = kernels.meandiff_compact(ct, bt_arg, mode, False, want_f32=True, want_norm=False)
+        s32, sr, _ = kernels.meandiff_compact(ct, bt_arg, mode, False, want_f32=True, want_norm=True)
+        _, wr_only, _ = kernels.meandiff_compact(ct, bt_arg, mode, False, want_f32=False, want_norm=False)
+        g32, gr, _ = kernels.gather_meandiff([ct[l].unsqueeze(1) for l in range(L)],
+                                             None if mode == "raw" else [bt[l].unsqueeze(1) for l in range(L)], mode, False,
+                                             want_norm=False)
+        torch.cuda.synchronize()
+        assert none is None
+        assert torch.equal(wr, sr) and torch.equal(w32, s32), (dt, mode, k)
+        assert torch.equal(wr_only, sr) and torch.equal(gr, sr) and torch.equal(g32, s32), (dt, mode, k)
+        for l in (0, L // 2, L - 1):
+            o32, orr, _ = K.meandiff(conc[l], base[l], mode, dt, False)
+            assert np.array_equal(wr[l].float().cpu().numpy(), orr), (dt, mode, k, l)
+            assert np.array_equal(w32[l].cpu().numpy(), o32), (dt, mode, k, l)
+    # gathered, with row and token indices
+    L, C, Nb, H, Tc, Tb = 16, 9, 60, 4096, 3, 4
+    conc, base = residual_batch(L, C, Tc, H, dt, 500), residual_batch(L, Nb, Tb, H, dt, 501)
+    rng = np.random.default_rng(7)
+    ctok, btok = rng.integers(0, Tc, size=C).astype(np.int32), rng.integers(0, Tb, size=Nb).astype(np.int32)
+    crow = rng.permutation(C).astype(np.int32)
+    cl, bl = [to_model(conc[l], dt, dev) for l in range(L)], [to_model(base[l], dt, dev) for l in range(L)]
+    if mode == "simple":
+        return
+    v32, vr, _ = kernels.gather_meandiff(cl, None if mode == "raw" else bl, mode, False, concept_rows=crow, concept_tok=ctok,
+                                         base_tok=btok, want_norm=False)
+    torch.cuda.synchronize()
+    for l in (0, L - 1):
+        o32, orr, _ = K.meandiff(conc[l][crow, ctok], base[l][np.arange(Nb), btok], mode, dt, False)
+        assert np.array_equal(vr[l].float().cpu().numpy(), orr) and np.array_equal(v32[l].cpu().numpy(), o32), (dt, mode, l)
