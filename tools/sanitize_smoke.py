@@ -2,7 +2,7 @@
 
 Covers what VERDICT r1 asked for: the bulk-copy ring with many wrap-arounds (700 x 3 x 256 vectors), the staged and
 loaded residual-add layouts, the Gemma-2 tail, the streaming kernel in all three forms (several trips round each
-warp's ring), the capture tap, K1 chunked / fused / compact, and two back-to-back ia_gather_meandiff_static calls on
+warp's ring), the capture tap, K1 chunked / fused / compact / column walker, and two back-to-back ia_gather_meandiff_static calls on
 one stream.
 """
 import os
@@ -74,6 +74,12 @@ for (L, C, Nb, H, T) in ((2, 5, 100, 896, 3), (1, 3, 700, 1024, 2), (3, 50, 100,
     for _ in range(2):  # back to back on one stream: the second call reuses the scratch the first one left
         rc = lib.ia_gather_meandiff_static(cptr.data_ptr(), T, 0, 0, C, bptr.data_ptr(), T, 0, 0, Nb, L, H, 0, 1, 0, outr.data_ptr(), 0, 0, 0)
         assert rc == 0
+# K1 column walker (n_layers * H >= 65536, no index arrays, no norm outputs): row counts on both sides of a 50-row request
+for (L, C, Nb, H) in ((16, 51, 100, 4096), (80, 3, 49, 896)):
+    ca = torch.randn(L, C, H, device=dev, generator=g).to(torch.bfloat16)
+    ba = torch.randn(L, Nb, H, device=dev, generator=g).to(torch.bfloat16)
+    kernels.meandiff_compact(ca, ba, "baseline", False, want_f32=True, want_norm=False)
+    kernels.meandiff_compact(ca, None, "raw", False, want_f32=False, want_norm=False)
 q = torch.randn(3, 9, 8 * 64, device=dev, generator=g).to(torch.bfloat16).view(3, 9, 8, 64).transpose(1, 2)
 k = torch.randn(3, 9, 2 * 64, device=dev, generator=g).to(torch.bfloat16).view(3, 9, 2, 64).transpose(1, 2)
 cs = torch.randn(3, 9, 64, device=dev, generator=g).to(torch.bfloat16)
