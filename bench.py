@@ -573,7 +573,7 @@ def run_ours(args):
         if parity is not None:
             line["parity_check"] = parity
         line.update(extras)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         torch.distributed.destroy_process_group()
 
@@ -724,7 +724,7 @@ def run_reference(args):
     value = rows * args.steps / dt
     threads = torch.get_num_threads()
     sample = _sample_text(rows, args.arch)
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": metric_name(args.arch), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random-init weights, stub-tokenised uniform ids)",
@@ -734,7 +734,31 @@ def run_reference(args):
                          "host_cpus": os.cpu_count()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }), flush=True)
+    })
+
+
+_REAL_STDOUT = None
+
+
+def _stdout_for_the_json_line_only():
+    """stdout carries the one JSON line and nothing else: whatever libraries print there meanwhile (NCCL's version banner
+    when the box sets NCCL_DEBUG=VERSION — a plain printf, NCCL_DEBUG_FILE does not move it) is sent to stderr by pointing
+    file descriptor 1 at stderr until `emit` puts it back."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+        os.close(_REAL_STDOUT)
+        _REAL_STDOUT = None
+    print(json.dumps(line), flush=True)
 
 
 def main():
@@ -756,6 +780,7 @@ def main():
                          "rows) instead of extracting from the whole prompt sets on every rank; faster, not rank-count-invariant in bits")
     ap.add_argument("--ncu-window", action="store_true", help="cudaProfilerStart at the last timed step (for ncu)")
     args = ap.parse_args()
+    _stdout_for_the_json_line_only()
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -17,9 +17,23 @@ def _run(args, timeout):
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *args], capture_output=True, text=True,
                          timeout=timeout, cwd=ROOT)
     assert out.returncode == 0, out.stderr[-2000:]
-    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
-    assert len(lines) == 1, out.stdout[-2000:]
+    lines = out.stdout.splitlines()
+    assert len(lines) == 1 and lines[0].startswith("{"), out.stdout[-2000:]  # ONE JSON line and nothing else on stdout
     return json.loads(lines[0])
+
+
+def test_stdout_carries_only_the_json_line():
+    """Whatever a library writes to file descriptor 1 while the bench runs (NCCL prints its version banner there when the
+    box sets NCCL_DEBUG=VERSION) must not reach the driver's pipe."""
+    code = ("import importlib.util, os\n"
+            "spec = importlib.util.spec_from_file_location('bench', 'bench.py'); b = importlib.util.module_from_spec(spec)\n"
+            "spec.loader.exec_module(b)\n"
+            "b._stdout_for_the_json_line_only()\n"
+            "os.write(1, b'NCCL version 2.28.9+cuda12.9\\n'); print('library chatter')\n"
+            "b.emit({'ok': 1})\n")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout == '{"ok": 1}\n' and "NCCL version" in out.stderr and "library chatter" in out.stderr
 
 
 def test_reference_arm_line_on_cpu():
