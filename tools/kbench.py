@@ -113,6 +113,54 @@ def bench_tail(rows, H, impl, reps, flush, dtype=torch.bfloat16):
                 gbs=algo / ms / 1e6, dram_gbs=dram / ms / 1e6)
 
 
+def bench_k2_graph(rows, H, form, reps, n_in_graph=64, n_sets=8, dtype=torch.bfloat16, impl="auto"):
+    """Small shapes as the decode loop runs them: `n_in_graph` launches captured back to back in ONE CUDA graph (rotating
+    over `n_sets` buffer sets, as consecutive layers do), replayed; us = replay time / launches.  The cold / hot figures of
+    the ladder at these sizes measure the launch, not the kernel ("the measured us inside a CUDA graph on
+    the small ones")."""
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(0)
+    lib = _lib.load()
+    vt = (torch.randn(50, H, device=dev, generator=g) * 0.1).to(dtype)
+    w = torch.ones(H, device=dev, dtype=dtype) if form != "tail" else torch.zeros(H, device=dev, dtype=dtype)
+    row_vec = (torch.arange(rows, device=dev) % 50).to(torch.int32)
+    alpha = torch.full((rows,), 4.0, device=dev)
+    t0 = torch.zeros(rows, device=dev, dtype=torch.int32)
+    sets = [[torch.randn(rows, 1, H, device=dev, generator=g).to(dtype) for _ in range(3)] for _ in range(n_sets)]
+    flags = _lib.IA_STEER_ALL | {"auto": 0, "tma": _lib.IA_IMPL_TMA, "regs": _lib.IA_IMPL_REGS, "stream": _lib.IA_IMPL_STREAM}[impl]
+
+    def launch(k, stream):
+        h, b, y = sets[k % n_sets]
+        if form == "plain":
+            rc = lib.ia_inject_rmsnorm(h.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(), t0.data_ptr(),
+                                       w.data_ptr(), 1e-5, rows, 1, H, 0, kernels._dt(h), kernels._dt(vt), kernels.VARIANTS["llama"], flags, stream)
+        elif form == "add":
+            rc = lib.ia_add_inject_rmsnorm(h.data_ptr(), b.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(),
+                                           t0.data_ptr(), w.data_ptr(), 1e-5, rows, 1, H, 0, kernels._dt(h), kernels._dt(vt),
+                                           kernels.VARIANTS["llama"], flags, stream)
+        else:
+            rc = lib.ia_gemma2_tail_inject_rmsnorm(b.data_ptr(), h.data_ptr(), y.data_ptr(), vt.data_ptr(), row_vec.data_ptr(), alpha.data_ptr(),
+                                                   t0.data_ptr(), w.data_ptr(), w.data_ptr(), 1e-6, rows, 1, H, 0, kernels._dt(h), kernels._dt(vt),
+                                                   flags, stream)
+        assert rc == 0, rc
+
+    launch(0, torch.cuda.current_stream().cuda_stream)  # set-up calls (shared-memory opt-in) happen outside the capture
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        st = torch.cuda.current_stream().cuda_stream
+        for k in range(n_in_graph):
+            launch(k, st)
+    ms = time_launch(graph.replay, reps, None)
+    e = sets[0][0].element_size()
+    streams = {"plain": 4, "add": 5, "tail": 5}[form]
+    algo = rows * H * e * streams + H * e
+    us = ms * 1e3 / n_in_graph
+    return dict(kernel={"plain": "k2_inject_rmsnorm", "add": "k2_add_inject_rmsnorm", "tail": "k2_gemma2_tail"}[form], impl=impl,
+                rows=rows, T=1, H=H, bytes=algo, us=us, gbs=algo / us / 1e3, cache="graph", launches_per_replay=n_in_graph,
+                note="back-to-back launches inside one CUDA graph replay, L2-resident operands (the decode loop's situation)")
+
+
 def bench_copy(nbytes, reps, flush):
     """torch's device copy moving `nbytes` in total (half read, half written), timed the same way: what the copy
     that defines MEASURED_PEAKS.json's hbm_gbs achieves at THIS size (launch ramp and tail included)."""
@@ -183,7 +231,7 @@ def main():
     ap.add_argument("--only-h", type=int, default=4096, help="with --only-rows")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only-rows", type=int, default=0, help="run a single cold K2 shape (for ncu --set full)")
-    ap.add_argument("--only-k1", action="store_true", help="run only the K1 ladder")
+    ap.add_argument("--only-k1", action="store_true", help="run only the K1 ladder (and, with --r2, the graph-timed small K2 shapes)")
     ap.add_argument("--add", action="store_true", help="K2 in its residual-add form (ia_add_inject_rmsnorm)")
     ap.add_argument("--add-staged", action="store_true", help="with --add: force the bulk-copied branch row (IA_IMPL_ADD_STAGED)")
     args = ap.parse_args()
@@ -206,6 +254,11 @@ def main():
                         emit(bench_tail(rows, H, impl, args.reps, flush))
             for nbytes in (rows * 4096 * 2 * 3, rows * 4096 * 2 * 4):
                 emit(bench_copy(nbytes, args.reps, flush))
+        for rows in (200, 3000):
+            for H, form in ((4096, "plain"), (4096, "add"), (5120, "add"), (3584, "tail")):
+                r = bench_k2_graph(rows, H, form, args.reps)
+                r.update(frac=r["gbs"] / peak, peak=peak, peak_src=src)
+                print(json.dumps(r), flush=True)
         for (L, C, Nb) in [(1, 50, 100), (32, 50, 100), (64, 50, 100), (1, 50, 16334), (1, 50, 262094)]:
             for want_norm in (False, True):
                 emit(bench_k1_compact(L, C, Nb, 4096, args.reps, flush, want_norm=want_norm))
