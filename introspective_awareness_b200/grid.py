@@ -106,15 +106,21 @@ def chunk(rows: Sequence[Trial], batch_size: int) -> Iterable[Sequence[Trial]]:
 
 
 def run_layer(model, layer_idx: int, vectors: Dict[str, torch.Tensor], rows: Sequence[Trial], max_new_tokens: int = 100,
-              temperature: float = 1.0, batch_size: int = 256, layer_fraction: Optional[float] = None) -> List[dict]:
+              temperature: float = 1.0, batch_size: int = 256, layer_fraction: Optional[float] = None,
+              only_batches: Optional[Sequence[int]] = None) -> List[dict]:
     """Generate every row of one layer and return result dicts in the reference's schema
-    (detect_injected_thoughts.py:1871-1881)."""
+    (detect_injected_thoughts.py:1871-1881).  `only_batches` restricts the call to those of the layer's batches
+    (indices into `chunk(rows, batch_size)`; the batches themselves are the same whoever runs them) — how a layer
+    left over by the round-robin deal is shared between ranks (sweep.run_sweep)."""
     concepts = list(vectors.keys())
     cidx = {c: i for i, c in enumerate(concepts)}
     table = torch.stack([vectors[c].reshape(-1) for c in concepts])
     results: List[dict] = []
     prompt_cache: Dict[tuple, tuple] = {}
-    for part in chunk(rows, batch_size):
+    wanted = None if only_batches is None else set(only_batches)
+    for b, part in enumerate(chunk(rows, batch_size)):
+        if wanted is not None and b not in wanted:
+            continue
         prompts, starts = [], []
         for r in part:
             key = (r.trial, r.kind == "forced_injection")

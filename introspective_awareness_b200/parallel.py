@@ -49,6 +49,16 @@ def shard_round_robin(items: Sequence, rank: int, world_size: int) -> List:
     return [x for i, x in enumerate(items) if i % world_size == rank]
 
 
+def shard_whole_and_shared(items: Sequence, world_size: int) -> Tuple[List[List], List]:
+    """(whole, shared): the first len(items) // world_size * world_size items dealt round-robin, `whole[r]` to rank r —
+    every rank the same number — and the `len(items) % world_size` left over, whose work is split between ALL ranks by
+    a finer unit (sweep.run_sweep splits a left-over layer's row batches): 42 Gemma-2 layers on 8 GPUs are 5 whole
+    layers each plus 2 shared ones instead of 6 / 5; one layer on 8 GPUs is shared by all eight."""
+    n_whole = len(items) // world_size * world_size
+    whole = [[x for i, x in enumerate(items[:n_whole]) if i % world_size == r] for r in range(world_size)]
+    return whole, list(items[n_whole:])
+
+
 def shard_contiguous(n: int, rank: int, world_size: int) -> Tuple[int, int]:
     """[lo, hi) of a contiguous, balanced split of n items (first n % world ranks get one more)."""
     base, extra = divmod(n, world_size)

@@ -12,7 +12,7 @@ What differs from the reference's sweep (detect_injected_thoughts.py:1551-1561, 
 all layer fractions are extracted from ONE pair of forwards (K1 over all layers), each layer's
 concept x strength x trial grid is ONE steered batch sequence with per-row strength (K2), control
 trials are generated once per layer instead of once per (layer, strength), and layers are dealt
-round-robin to the ranks of a `torch.distributed` job.  The LLM judge stays outside (host-side,
+round-robin to the ranks of a `torch.distributed` job (left-over layers shared batch by batch).  The LLM judge stays outside (host-side,
 untimed): metrics here are the reference's keyword metrics (`check_concept_mentioned`).
 """
 
@@ -86,8 +86,11 @@ def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], lay
     then n_injection + t, then n_injection + n_control + t (detect_injected_thoughts.py:1792-1799, :1917, :1984).
 
     In a `torch.distributed` job (one process per GPU, `parallel.init_from_env`) this is a collective call: each
-    rank steers the layer fractions dealt to it round-robin and writes their files, and the result rows are
-    gathered — rank 0 returns every configuration, the other ranks their own.  Extraction: by default every rank
+    rank steers the layer fractions dealt to it round-robin — the same number for every rank — and writes their
+    files; the fractions left over (n % world; all of them when there are fewer layers than ranks) are shared, their
+    row batches dealt over all ranks and put together and written by rank 0 (42 Gemma-2 layers on 8 GPUs: 5 whole
+    layers per rank + 2 shared, not 6 / 5).  The result rows are gathered — rank 0 returns every configuration, the
+    other ranks those of their whole layers.  Extraction: by default every rank
     extracts the layers IT steers from the whole prompt sets (the reference's batch composition, hence the
     reference's vectors whatever the rank count; rank 0 also extracts what it needs for the vector files);
     sharded_extraction=True splits the prompts over the ranks instead (fp32 sums all-reduced, concept rows
@@ -99,12 +102,13 @@ def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], lay
     fractions = list(layer_fractions)
     layer_of = {f: get_layer_at_fraction(model, f) for f in fractions}
     uniq_layers = sorted(set(layer_of.values()))
-    mine = parallel.shard_round_robin(fractions, rank, world)
+    whole, shared = parallel.shard_whole_and_shared(fractions, world)
+    mine = whole[rank]
     if sharded_extraction and world > 1:
         need = uniq_layers
     else:
         keep_all = rank == 0 and output_dir is not None and save_vector_files
-        need = uniq_layers if keep_all else sorted({layer_of[f] for f in mine})
+        need = uniq_layers if keep_all else sorted({layer_of[f] for f in mine + shared})
     by_layer = vu.extract_concept_vectors_multi_layer(model, concepts, list(baseline_words), need,
                                                       extraction_method=extraction_method,
                                                       sharded=sharded_extraction and world > 1) if need else {}
@@ -116,25 +120,50 @@ def run_sweep(model, concepts: Sequence[str], baseline_words: Sequence[str], lay
                 save_vectors(base, f, by_layer[layer_of[f]])
     n_inj = n_trials // 2
     n_ctl = n_trials - n_inj
+    rows = grid.layer_trials(concepts, strengths, n_inj, n_ctl, n_inj if with_forced else 0, dedupe_control=True)
+
+    def configurations(f, results) -> Dict[tuple, List[dict]]:
+        """One entry (and one pair of files) per (layer fraction, strength), rows in the driver's order: injection,
+        control, forced (:1797-1799); the strength-independent control trials are stored in every strength's file."""
+        control = [r for r in results if r["trial_type"] == "control"]
+        cfgs = {}
+        for a in strengths:
+            steered = [r for r in results if r["trial_type"] != "control" and r["strength"] == float(a)]
+            cfg = [r for r in steered if r["trial_type"] == "injection"]
+            cfg += [dict(r, strength=float(a)) for r in control]
+            cfg += [r for r in steered if r["trial_type"] == "forced_injection"]
+            cfgs[(f, float(a))] = cfg
+            if base is not None:
+                write_config(base, f, layer_of[f], float(a), cfg, temperature, max_new_tokens)
+        return cfgs
+
     out: Dict[tuple, List[dict]] = {}
     for f in mine:
-        layer = layer_of[f]
-        rows = grid.layer_trials(concepts, strengths, n_inj, n_ctl, n_inj if with_forced else 0, dedupe_control=True)
-        results = grid.run_layer(model, layer, by_layer[layer], rows, max_new_tokens, temperature, batch_size,
-                                 layer_fraction=f)
-        control = [r for r in results if r["trial_type"] == "control"]
-        for a in strengths:
-            # one file per (layer fraction, strength), rows in the driver's order: injection, control, forced
-            # (:1797-1799); the strength-independent control trials are stored in every strength's file
-            mine = [r for r in results if r["trial_type"] != "control" and r["strength"] == float(a)]
-            cfg = [r for r in mine if r["trial_type"] == "injection"]
-            cfg += [dict(r, strength=float(a)) for r in control]
-            cfg += [r for r in mine if r["trial_type"] == "forced_injection"]
-            out[(f, float(a))] = cfg
-            if base is not None:
-                write_config(base, f, layer, float(a), cfg, temperature, max_new_tokens)
+        out.update(configurations(f, grid.run_layer(model, layer_of[f], by_layer[layer_of[f]], rows, max_new_tokens,
+                                                    temperature, batch_size, layer_fraction=f)))
+    # the layers the round-robin deal leaves over: their row batches are dealt over ALL ranks (batch u of the list of
+    # (layer, batch) units to rank u % world), gathered, and put together — and written — by rank 0
+    n_batches = len(list(grid.chunk(rows, batch_size)))
+    units = [(f, b) for f in shared for b in range(n_batches)]
+    pieces: Dict[tuple, List[dict]] = {}
+    for f in shared:
+        my_batches = [b for u, (g, b) in enumerate(units) if g == f and u % world == rank]
+        if not my_batches:
+            continue
+        got = grid.run_layer(model, layer_of[f], by_layer[layer_of[f]], rows, max_new_tokens, temperature, batch_size,
+                             layer_fraction=f, only_batches=my_batches)
+        sizes = [len(part) for k, part in enumerate(grid.chunk(rows, batch_size)) if k in set(my_batches)]
+        at = 0
+        for b, n in zip(my_batches, sizes):
+            pieces[(f, b)] = got[at:at + n]
+            at += n
     if world > 1:
-        parts = parallel.gather_objects_to_rank0(out)
+        parts = parallel.gather_objects_to_rank0((out, pieces))
         if rank == 0:
-            out = {k: v for part in parts for k, v in part.items()}
+            out = {k: v for part, _ in parts for k, v in part.items()}
+            pieces = {k: v for _, part in parts for k, v in part.items()}
+    if rank == 0:
+        for f in shared:
+            out.update(configurations(f, [r for b in range(n_batches) for r in pieces[(f, b)]]))
+        out = {(f, float(a)): out[(f, float(a))] for f in fractions for a in strengths}  # the caller's order
     return out

@@ -25,6 +25,12 @@ def test_sharding_helpers():
         lo, hi = parallel.shard_contiguous(42, r, 5)
         cover += list(range(lo, hi))
     assert cover == list(range(42))  # Gemma-2's 42 layers over 5 ranks: every layer exactly once
+    # the sweep's deal: the same number of whole layers for every rank, the left-over ones shared batch by batch
+    whole, shared = parallel.shard_whole_and_shared(list(range(42)), 8)
+    assert [len(w) for w in whole] == [5] * 8 and shared == [40, 41] and whole[3] == [3, 11, 19, 27, 35]
+    assert sorted(x for w in whole for x in w) + shared == list(range(42))
+    assert parallel.shard_whole_and_shared([7], 8) == ([[] for _ in range(8)], [7])  # one layer on 8 GPUs: shared by all
+    assert parallel.shard_whole_and_shared(list(range(32)), 8)[1] == [] and parallel.shard_whole_and_shared([1, 2], 1) == ([[1, 2]], [])
 
 
 def _free_port():
@@ -95,6 +101,12 @@ def _worker(rank, world, port, out_dir):
     assert set(res) == ({(f, a) for f in (0.2, 0.5, 0.8) for a in (2.0, 8.0)} if rank == 0 else mine)
     if rank == 0:
         torch.save(res, os.path.join(out_dir, "sweep_rank0.pt"))
+    # fewer layers than ranks: the one layer's row batches are shared between the ranks, rank 0 puts them together
+    res1 = sweep.run_sweep(ScriptedModel(chat=True), ["Dust", "Trees", "Oceans"], vu.get_baseline_words(4), [0.5], [2.0, 8.0], n_trials=5,
+                           max_new_tokens=5, temperature=0.0, batch_size=4, output_dir=os.path.join(out_dir, "sweep1"))
+    assert set(res1) == ({(0.5, 2.0), (0.5, 8.0)} if rank == 0 else set())
+    if rank == 0:
+        torch.save(res1, os.path.join(out_dir, "sweep1_rank0.pt"))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -116,6 +128,18 @@ def test_world_size_2_gloo(tmp_path):
     one = sweep.run_sweep(ScriptedModel(chat=True), ["Dust", "Trees"], vu.get_baseline_words(4), [0.2, 0.5, 0.8], [2.0, 8.0],
                           n_trials=4, max_new_tokens=5, temperature=0.0, batch_size=8, output_dir=str(tmp_path / "single"))
     assert two == one
+    assert list(two) == list(one)  # and in the caller's order
     for (f, a), rows in one.items():
         blob = json.load(open(tmp_path / "sweep" / "spy_model" / f"layer_{f:.2f}_strength_{a}" / "results.json"))
         assert blob["results"] == rows
+    # 0.2 and 0.5 were whole layers of rank 0 / rank 1, 0.8 was shared batch by batch; a single shared layer likewise
+    shared = torch.load(tmp_path / "sweep1_rank0.pt")
+    alone = sweep.run_sweep(ScriptedModel(chat=True), ["Dust", "Trees", "Oceans"], vu.get_baseline_words(4), [0.5], [2.0, 8.0],
+                            n_trials=5, max_new_tokens=5, temperature=0.0, batch_size=4, output_dir=str(tmp_path / "single1"))
+    assert shared == alone and len(alone[(0.5, 2.0)]) == 3 * (2 + 3 + 2)
+    for (f, a), rows in alone.items():
+        for root in ("sweep1", "single1"):
+            blob = json.load(open(tmp_path / root / "spy_model" / f"layer_{f:.2f}_strength_{a}" / "results.json"))
+            assert blob["results"] == rows
+        assert (open(tmp_path / "sweep1" / "spy_model" / f"layer_{f:.2f}_strength_{a}" / "results.csv").read()
+                == open(tmp_path / "single1" / "spy_model" / f"layer_{f:.2f}_strength_{a}" / "results.csv").read())

@@ -52,11 +52,11 @@ def _worker(rank, world, port, out_dir):
     # the sweep as a collective call: default (every rank extracts its own layers from the whole prompt sets: the
     # one-process bits) and with prompt-sharded extraction
     for tag, sharded in (("two", False), ("two_sharded", True)):
-        res = sweep.run_sweep(m, ["Dust", "Trees", "Oceans"], vu.get_baseline_words(6), [0.3, 0.8], [2.0, 8.0], n_trials=4,
-                              max_new_tokens=5, temperature=0.0, batch_size=16, output_dir=os.path.join(out_dir, tag),
+        res = sweep.run_sweep(m, ["Dust", "Trees", "Oceans"], vu.get_baseline_words(6), [0.3, 0.6, 0.8], [2.0, 8.0], n_trials=4,
+                              max_new_tokens=5, temperature=0.0, batch_size=8, output_dir=os.path.join(out_dir, tag),
                               sharded_extraction=sharded)
         if rank == 0:
-            assert set(res) == {(f, a) for f in (0.3, 0.8) for a in (2.0, 8.0)}
+            assert set(res) == {(f, a) for f in (0.3, 0.6, 0.8) for a in (2.0, 8.0)}
             torch.save(res, os.path.join(out_dir, tag + ".pt"))
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
@@ -72,8 +72,9 @@ def test_world_size_2_nccl(tmp_path):
     two, two_sharded = torch.load(tmp_path / "two.pt"), torch.load(tmp_path / "two_sharded.pt")
     m = ModelWrapper.from_arch("tiny-llama", device="cuda:0", dtype=torch.bfloat16, seed=13)
     m.model_name = "tiny/llama"
-    one = sweep.run_sweep(m, ["Dust", "Trees", "Oceans"], vu.get_baseline_words(6), [0.3, 0.8], [2.0, 8.0], n_trials=4,
-                          max_new_tokens=5, temperature=0.0, batch_size=16, output_dir=str(tmp_path / "one"))
+    one = sweep.run_sweep(m, ["Dust", "Trees", "Oceans"], vu.get_baseline_words(6), [0.3, 0.6, 0.8], [2.0, 8.0], n_trials=4,
+                          max_new_tokens=5, temperature=0.0, batch_size=8, output_dir=str(tmp_path / "one"))
+    # 0.3 / 0.6 are whole layers of rank 0 / rank 1, 0.8 is left over and shared batch by batch (rank 0 puts it together)
     assert two == one  # default extraction: every rank works from the whole prompt sets, so the one-process results exactly
     for k in sorted(one):
         assert torch.equal(torch.load(tmp_path / "two" / "tiny_llama" / "vectors" / f"layer_{k[0]:.2f}" / "Trees.pt"),
