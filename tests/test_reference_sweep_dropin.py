@@ -130,12 +130,13 @@ def _no_reference_modules_left_behind():
 
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(REF, "detect_injected_thoughts.py")), reason="reference not mounted")
-@pytest.mark.parametrize("chat,model_name", [(False, "spy_model"), (True, "spy_model"), (True, "gemma2_9b")])
-def test_sweep_equals_the_real_drivers_sweep(monkeypatch, tmp_path, chat, model_name):
+@pytest.mark.parametrize("chat,model_name,n_trials,batch", [(False, "spy_model", 5, 4), (True, "spy_model", 5, 4),
+                                                            (True, "gemma2_9b", 5, 4), (True, "spy_model", 4, 7)])
+def test_sweep_equals_the_real_drivers_sweep(monkeypatch, tmp_path, chat, model_name, n_trials, batch):
     from introspective_awareness_b200 import sweep, vector_utils as vu
 
     concepts, fractions, strengths = ["Dust", "Trees", "Oceans"], [0.3, 0.8], [2.0, 8.0]
-    n_trials, n_base, max_tokens, batch = 5, 6, 7, 4
+    n_base, max_tokens = 6, 7
 
     # ---- the reference driver, unmodified, in sweep mode ---------------------------------------
     drv = _load_driver(monkeypatch)
