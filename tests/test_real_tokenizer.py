@@ -181,7 +181,7 @@ def test_sweep_equals_the_real_drivers_sweep_with_a_real_tokenizer(monkeypatch, 
             self.tokenizer = tok
 
     monkeypatch.setattr(T, "ScriptedModel", RealTokModel)
-    T.test_sweep_equals_the_real_drivers_sweep(monkeypatch, tmp_path, True, name)
+    T.test_sweep_equals_the_real_drivers_sweep(monkeypatch, tmp_path, True, name, 5, 4)
 
 
 @pytest.mark.gpu
